@@ -1,0 +1,310 @@
+// TEST INFRASTRUCTURE ONLY -- the "reference" leg of the parity oracle.  Never linked into, imported by, or called from the
+// product library (teqp_b200/); only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use it.
+//
+// What this is: a flat C API, batched over state points with std::thread, in front of the reference's OWN type-erased
+// interface teqp::cppinterface::AbstractModel (/root/reference/include/teqp/cpp/teqpcpp.hpp:94-191), whose implementation
+// DerivativeAdapter<> (/root/reference/include/teqp/cpp/deriv_adapter.hpp:106-248) and model factories
+// (/root/reference/interface/CPP/model_factory_{GERG,pcsaft,SAFTVRMie,genericsaft}.cpp) are compiled from the sources where
+// they lie.  Every value returned by this file was computed by the reference's model templates and derivative drivers
+// (/root/reference/include/teqp/derivs.hpp); the only restated piece is the forward-mode AD engine (oracle/shim/), because
+// autodiff @ cb2d6e8b is absent from the reference tree (/root/reference/.SUBMODULES.json:44-50).
+//
+// The kind -> factory map below restates the subset of /root/reference/interface/CPP/teqp_impl_factory.cpp:54-102 that is in
+// scope (that TU itself cannot be used: it references all 35 factories and the cmake-generated schema library).
+#include "teqp/cpp/teqpcpp.hpp"
+#include "teqp/cpp/deriv_adapter.hpp"
+#include "teqp/models/vdW.hpp"
+#include "teqp/models/cubics/simple_cubics.hpp"
+#include "teqp/models/GERG/GERG.hpp"
+#include "teqp/models/pcsaft.hpp"
+
+#include <thread>
+#include <vector>
+#include <cstring>
+#include <string>
+#include <functional>
+#include <atomic>
+
+namespace teqp { namespace cppinterface {
+    std::unique_ptr<AbstractModel> make_SAFTVRMie(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_PCSAFT(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_genericSAFT(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_GERG2004resid(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_GERG2008resid(const nlohmann::json &);
+}}
+
+using namespace teqp;
+using namespace teqp::cppinterface;
+using teqp::cppinterface::adapter::make_owned;
+
+namespace {
+
+struct RefModel {
+    std::unique_ptr<AbstractModel> am;
+    std::string kind;
+};
+
+std::unique_ptr<AbstractModel> build(const nlohmann::json& j, std::string& kind) {
+    kind = j.at("kind").get<std::string>();
+    const auto& spec = j.at("model");
+    if (kind == "vdW1") return make_owned(vdWEOS1(spec.at("a"), spec.at("b")));
+    if (kind == "vdW") return make_owned(vdWEOS<double>(spec.at("Tcrit / K"), spec.at("pcrit / Pa")));
+    if (kind == "PR") return make_owned(make_canonicalPR(spec));
+    if (kind == "SRK") return make_owned(make_canonicalSRK(spec));
+    if (kind == "cubic") return make_owned(make_generalizedcubic(spec));
+    if (kind == "PCSAFT") return make_PCSAFT(spec);
+    if (kind == "SAFT-VR-Mie") return make_SAFTVRMie(spec);
+    if (kind == "genericSAFT") return make_genericSAFT(spec);
+    if (kind == "GERG2004resid") return make_GERG2004resid(spec);
+    if (kind == "GERG2008resid") return make_GERG2008resid(spec);
+    throw std::invalid_argument("Don't understand \"kind\" of: " + kind);
+}
+
+void put_err(const std::string& msg, char* err, int errlen) {
+    if (err && errlen > 0) { std::strncpy(err, msg.c_str(), errlen - 1); err[errlen - 1] = 0; }
+}
+
+// static contiguous partition of [0,npts) over nthreads; fn(k) evaluates point k.  First exception wins.
+template<typename F>
+int parallel_points(long long npts, int nthreads, char* err, int errlen, F&& fn) {
+    if (nthreads < 1) nthreads = 1;
+    if ((long long)nthreads > npts) nthreads = (int)std::max<long long>(1, npts);
+    std::vector<std::thread> th;
+    std::atomic<int> failed{0};
+    std::string msg;
+    std::mutex mtx;
+    auto body = [&](long long lo, long long hi) {
+        try { for (long long k = lo; k < hi; ++k) fn(k); }
+        catch (const std::exception& e) { std::lock_guard<std::mutex> g(mtx); if (!failed) { failed = 1; msg = e.what(); } }
+    };
+    const long long chunk = (npts + nthreads - 1) / nthreads;
+    for (int t = 0; t < nthreads; ++t) {
+        long long lo = t * chunk, hi = std::min(npts, lo + chunk);
+        if (lo >= hi) break;
+        if (nthreads == 1) body(lo, hi); else th.emplace_back(body, lo, hi);
+    }
+    for (auto& t : th) t.join();
+    if (failed) { put_err(msg, err, errlen); return 9999; }
+    return 0;
+}
+
+inline void gather(const double* soa, long long npts, long long k, int n, Eigen::ArrayXd& z) {
+    for (int i = 0; i < n; ++i) z[i] = soa[(long long)i * npts + k];
+}
+
+} // namespace
+
+#define REF_TRY try {
+#define REF_CATCH } catch (const std::exception& e) { put_err(e.what(), err, errlen); return 9999; }
+
+extern "C" {
+
+void* ref_build_model(const char* json, char* err, int errlen) {
+    try {
+        auto m = new RefModel();
+        m->am = build(nlohmann::json::parse(json), m->kind);
+        return m;
+    } catch (const std::exception& e) { put_err(e.what(), err, errlen); return nullptr; }
+}
+void ref_free_model(void* h) { delete static_cast<RefModel*>(h); }
+
+int ref_get_R(void* h, const double* z, int ncomp, double* out, char* err, int errlen) {
+    REF_TRY
+    Eigen::ArrayXd zz = Eigen::Map<const Eigen::ArrayXd>(z, ncomp);
+    *out = static_cast<RefModel*>(h)->am->get_R(zz);
+    return 0;
+    REF_CATCH
+}
+
+// out[(nmax+1)][npts]: AbstractModel::get_Ar0{nmax}n (teqpcpp.hpp:111-113) per point
+int ref_get_Ar0n(void* h, int nmax, long long npts, const double* T, const double* rho, const double* x, int ncomp,
+                 double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    if (nmax < 1 || nmax > 6) { put_err("nmax must be 1..6", err, errlen); return 1; }
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        Eigen::ArrayXd v;
+        switch (nmax) {
+            case 1: v = am.get_Ar01n(T[k], rho[k], z); break;
+            case 2: v = am.get_Ar02n(T[k], rho[k], z); break;
+            case 3: v = am.get_Ar03n(T[k], rho[k], z); break;
+            case 4: v = am.get_Ar04n(T[k], rho[k], z); break;
+            case 5: v = am.get_Ar05n(T[k], rho[k], z); break;
+            default: v = am.get_Ar06n(T[k], rho[k], z); break;
+        }
+        for (int n = 0; n <= nmax; ++n) out[(long long)n * npts + k] = v[n];
+    });
+}
+
+// out[(nmax+1)][npts]: AbstractModel::get_Ar{nmax}0n (teqpcpp.hpp:115-117)
+int ref_get_Arn0(void* h, int nmax, long long npts, const double* T, const double* rho, const double* x, int ncomp,
+                 double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    if (nmax < 1 || nmax > 4) { put_err("nmax must be 1..4", err, errlen); return 1; }
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        Eigen::ArrayXd v;
+        switch (nmax) {
+            case 1: v = am.get_Ar10n(T[k], rho[k], z); break;
+            case 2: v = am.get_Ar20n(T[k], rho[k], z); break;
+            case 3: v = am.get_Ar30n(T[k], rho[k], z); break;
+            default: v = am.get_Ar40n(T[k], rho[k], z); break;
+        }
+        for (int n = 0; n <= nmax; ++n) out[(long long)n * npts + k] = v[n];
+    });
+}
+
+// compile-time-dispatched single derivative get_Ar{NT}{ND} (teqpcpp.hpp:107-109), NT in 0..2, ND in 0..4
+int ref_get_ArNM(void* h, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, int ncomp,
+                 double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    using Fn = double (AbstractModel::*)(const double, const double, const REArrayd&) const;
+    Fn fn = nullptr;
+#define X(i,j) if (NT == i && ND == j) fn = &AbstractModel::get_Ar ## i ## j;
+    ARXY_args
+#undef X
+    if (!fn) { put_err("unsupported (NT,ND) for get_ArNM", err, errlen); return 1; }
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        out[k] = (am.*fn)(T[k], rho[k], z);
+    });
+}
+
+// runtime-dispatched get_Arxy (teqpcpp.hpp:104; derivs.hpp:627-682), what the reference C ABI calls (teqpc.cpp:105-117)
+int ref_get_Arxy(void* h, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, int ncomp,
+                 double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        out[k] = am.get_Arxy(NT, ND, T[k], rho[k], z);
+    });
+}
+
+int ref_get_ATrhoXi(void* h, int NT, int ND, int i, int NXi, long long npts, const double* T, const double* rho, const double* x,
+                    int ncomp, double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        out[k] = am.get_ATrhoXi(T[k], NT, rho[k], ND, z, i, NXi);
+    });
+}
+int ref_get_ATrhoXiXj(void* h, int NT, int ND, int i, int NXi, int j, int NXj, long long npts, const double* T, const double* rho,
+                      const double* x, int ncomp, double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        out[k] = am.get_ATrhoXiXj(T[k], NT, rho[k], ND, z, i, NXi, j, NXj);
+    });
+}
+int ref_get_ATrhoXiXjXk(void* h, int NT, int ND, int i, int NXi, int j, int NXj, int kk, int NXk, long long npts, const double* T,
+                        const double* rho, const double* x, int ncomp, double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        out[k] = am.get_ATrhoXiXjXk(T[k], NT, rho[k], ND, z, i, NXi, j, NXj, kk, NXk);
+    });
+}
+
+// Isochoric family (teqpcpp.hpp:52-75; deriv_adapter.hpp:226-241).  rhovec is SoA [ncomp][npts].
+// what: 0 get_pr, 1 get_splus, 2 get_dpdT_constrhovec                                   -> out[npts]
+int ref_isochoric_scalar(void* h, int what, long long npts, const double* T, const double* rhovec, int ncomp, double* out,
+                         int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd r; if (r.size() != ncomp) r.resize(ncomp);
+        gather(rhovec, npts, k, ncomp, r);
+        out[k] = (what == 0) ? am.get_pr(T[k], r) : (what == 1) ? am.get_splus(T[k], r) : am.get_dpdT_constrhovec(T[k], r);
+    });
+}
+// what: 0 build_Psir_gradient_autodiff, 1 get_chempotVLE_autodiff, 2 get_dchempotdT_autodiff, 3 get_fugacity_coefficients,
+//       4 get_partial_molar_volumes, 5 build_d2PsirdTdrhoi_autodiff, 6 get_dpdrhovec_constT -> out[ncomp][npts]
+int ref_isochoric_array(void* h, int what, long long npts, const double* T, const double* rhovec, int ncomp, double* out,
+                        int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    if (what < 0 || what > 6) { put_err("bad selector", err, errlen); return 1; }
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd r; if (r.size() != ncomp) r.resize(ncomp);
+        gather(rhovec, npts, k, ncomp, r);
+        Eigen::ArrayXd v;
+        switch (what) {
+            case 0: v = am.build_Psir_gradient_autodiff(T[k], r); break;
+            case 1: v = am.get_chempotVLE_autodiff(T[k], r); break;
+            case 2: v = am.get_dchempotdT_autodiff(T[k], r); break;
+            case 3: v = am.get_fugacity_coefficients(T[k], r); break;
+            case 4: v = am.get_partial_molar_volumes(T[k], r); break;
+            case 5: v = am.build_d2PsirdTdrhoi_autodiff(T[k], r); break;
+            default: v = am.get_dpdrhovec_constT(T[k], r); break;
+        }
+        for (int i = 0; i < ncomp; ++i) out[(long long)i * npts + k] = v[i];
+    });
+}
+// build_Psir_fgradHessian_autodiff: f[npts], g[ncomp][npts], H[ncomp*ncomp][npts] (row-major index i*ncomp+j). Any may be null.
+// psi_total != 0 adds the ideal-gas diagonal, i.e. build_Psi_Hessian_autodiff (derivs.hpp:1076-1084), to H only.
+int ref_Psir_fgradHessian(void* h, int psi_total, long long npts, const double* T, const double* rhovec, int ncomp, double* f,
+                          double* g, double* H, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd r; if (r.size() != ncomp) r.resize(ncomp);
+        gather(rhovec, npts, k, ncomp, r);
+        auto [fv, gv, Hv] = am.build_Psir_fgradHessian_autodiff(T[k], r);
+        if (f) f[k] = fv;
+        if (g) for (int i = 0; i < ncomp; ++i) g[(long long)i * npts + k] = gv[i];
+        if (H) {
+            if (psi_total) { Eigen::ArrayXXd Ht = am.build_Psi_Hessian_autodiff(T[k], r); for (int i = 0; i < ncomp; ++i) for (int j = 0; j < ncomp; ++j) H[(long long)(i * ncomp + j) * npts + k] = Ht(i, j); }
+            else for (int i = 0; i < ncomp; ++i) for (int j = 0; j < ncomp; ++j) H[(long long)(i * ncomp + j) * npts + k] = Hv(i, j);
+        }
+    });
+}
+
+// ln(phi) and its derivatives are template-only in the reference (derivs.hpp:1219-1230, 1306-1393; not in AbstractModel), so
+// they need the concrete model type: recovered with get_model_cref<> (deriv_adapter.hpp:279-296) for the kinds listed.
+// what: 0 ln phi [ncomp], 1 d ln phi/dT|rhovec [ncomp], 2 d ln phi/drho|T,x [ncomp], 3 d ln phi_i/dx_j|T,rho [ncomp*ncomp], 4 d ln phi/dv|T,x
+} // extern "C"
+template<typename Model>
+void lnphi_point(const Model& model, int what, double T, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) {
+    using iso = IsochoricDerivatives<const Model&, double, Eigen::ArrayXd>;
+    switch (what) {
+        case 0: v = iso::get_ln_fugacity_coefficients(model, T, r); break;
+        case 1: v = iso::get_d_ln_fugacity_coefficients_dT_constrhovec(model, T, r); break;
+        case 2: v = iso::get_d_ln_fugacity_coefficients_drho_constTmolefracs(model, T, r); break;
+        case 4: v = iso::get_d_ln_fugacity_coefficients_dv_constTmolefracs(model, T, r); break;
+        default: {
+            Eigen::ArrayXXd M = iso::get_d_ln_fugacity_coefficients_dmolefracs_constTrho(model, T, r);
+            const int n = (int)r.size(); v.resize(n * n);
+            for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) v[i * n + j] = M(i, j);
+        }
+    }
+}
+extern "C" {
+int ref_lnphi_family(void* h, int what, long long npts, const double* T, const double* rhovec, int ncomp, double* out,
+                     int nthreads, char* err, int errlen) {
+    REF_TRY
+    auto* rm = static_cast<RefModel*>(h);
+    const AbstractModel* am = rm->am.get();
+    const int nout = (what == 3) ? ncomp * ncomp : ncomp;
+    std::function<void(double, const Eigen::ArrayXd&, Eigen::ArrayXd&)> one;
+    using namespace teqp::cppinterface::adapter;
+    if (rm->kind == "GERG2008resid") { const auto& m = get_model_cref<GERG2008::GERG2008ResidualModel>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "GERG2004resid") { const auto& m = get_model_cref<GERG2004::GERG2004ResidualModel>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "PR" || rm->kind == "SRK" || rm->kind == "cubic") { using M = decltype(make_canonicalPR(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "PCSAFT") { using M = decltype(PCSAFT::PCSAFTfactory(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else { put_err("ln(phi) family: kind not wired in the oracle: " + rm->kind, err, errlen); return 200; }
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd r, v; if (r.size() != ncomp) r.resize(ncomp);
+        gather(rhovec, npts, k, ncomp, r);
+        one(T[k], r, v);
+        for (int i = 0; i < nout; ++i) out[(long long)i * npts + k] = v[i];
+    });
+    REF_CATCH
+}
+
+int ref_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+} // extern "C"
