@@ -1,0 +1,101 @@
+/* libteqpb200 -- C ABI of the B200-native batched equation-of-state evaluator.
+ *
+ * Part 1 is the reference's extern "C" interface, exported with identical names, argument order, ownership and error
+ * conventions (/root/reference/interface/C/teqpc.h:2-20, implementation /root/reference/interface/C/teqpc.cpp:75-225), so that
+ * existing ctypes / FFI callers (e.g. /root/reference/interface/C/test_teqpc.py) bind to this library unchanged.  Scalar
+ * calls are evaluated ON THE GPU as a batch of one state point: there is no CPU evaluation path in this library.
+ *
+ * Part 2 adds the batched entry points (proposal in SURVEY.md section 8b): structure-of-arrays buffers owned by the caller,
+ * int return code (0 = OK), message copied into errmsg with the reference's truncation rules.
+ *
+ * Conventions for part 2
+ *   - T[npts], rho[npts]; molefrac[Ncomp][npts] (row i = component i, row stride npts), or molefrac[Ncomp] for every point
+ *     when TEQPB200_BROADCAST_X is set; rhovec[Ncomp][npts] for the isochoric family.
+ *   - outputs are [rows][npts] with row stride npts.
+ *   - flags & TEQPB200_DEVICE_PTRS: all data pointers are device pointers on the CURRENT CUDA device; the call enqueues on
+ *     the stream set with teqpb200_set_stream() (default: the legacy default stream) and returns without synchronising.
+ *     Otherwise the pointers are host pointers (pinned memory from teqpb200_host_alloc() makes the copies asynchronous);
+ *     the batch is split evenly over the devices chosen with teqpb200_set_devices(), streamed through each device in
+ *     chunks with copies overlapped with compute, and the call returns when all results are in the output buffers.
+ */
+#ifndef TEQPB200_H
+#define TEQPB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------- Part 1: the reference C ABI (teqpc.h:2-20) ---------------- */
+int build_model(const char* j, long long int* uuid, char* errmsg, int errmsg_length);                       /* teqpc.h:2  */
+int free_model(const long long int uuid, char* errmsg, int errmsg_length);                                  /* teqpc.h:4  */
+int get_Arxy(const long long int uuid, const int NT, const int ND, const double T, const double rho,
+             const double* molefrac, const int Ncomp, double* val, char* errmsg, int errmsg_length);         /* teqpc.h:6  */
+int get_ATrhoXi(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND,
+                const double* molefrac, const int Ncomp, const int i, const int NXi, double* val,
+                char* errmsg, int errmsg_length);                                                            /* teqpc.h:8  */
+int get_ATrhoXiXj(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND,
+                  const double* molefrac, const int Ncomp, const int i, const int NXi, const int j, const int NXj,
+                  double* val, char* errmsg, int errmsg_length);                                             /* teqpc.h:10 */
+int get_ATrhoXiXjXk(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND,
+                    const double* molefrac, const int Ncomp, const int i, const int NXi, const int j, const int NXj,
+                    const int k, const int NXk, double* val, char* errmsg, int errmsg_length);              /* teqpc.h:12 */
+int get_AtaudeltaXi(const long long int uuid, const double tau, const int Ntau, const double delta, const int Ndelta,
+                    const double* molefrac, const int Ncomp, const int i, const int NXi, double* val,
+                    char* errmsg, int errmsg_length);                                                        /* teqpc.h:14 */
+int get_AtaudeltaXiXj(const long long int uuid, const double tau, const int Ntau, const double delta, const int Ndelta,
+                      const double* molefrac, const int Ncomp, const int i, const int NXi, const int j, const int NXj,
+                      double* val, char* errmsg, int errmsg_length);                                         /* teqpc.h:16 */
+int get_AtaudeltaXiXjXk(const long long int uuid, const double tau, const int Ntau, const double delta, const int Ndelta,
+                        const double* molefrac, const int Ncomp, const int i, const int NXi, const int j, const int NXj,
+                        const int k, const int NXk, double* val, char* errmsg, int errmsg_length);          /* teqpc.h:18 */
+int get_dmBnvirdTm(const long long int uuid, const int Nvir, const int NT, const double T, const double* molefrac,
+                   const int Ncomp, double* val, char* errmsg, int errmsg_length);                           /* teqpc.h:20 */
+
+/* ---------------- Part 2: batched entry points ---------------- */
+#define TEQPB200_DEVICE_PTRS 1
+#define TEQPB200_BROADCAST_X 2
+
+/* AbstractModel::get_Ar0{nmax}n (teqpcpp.hpp:111-113; derivs.hpp:543-569,621-624): out[n][k] = rho^n d^n alphar/drho^n, n = 0..nmax (nmax 0..6) */
+int get_Ar0n_batch(const long long int uuid, const int nmax, const long long int npts, const double* T, const double* rho,
+                   const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+/* AbstractModel::get_Ar{nmax}0n (teqpcpp.hpp:115-117; derivs.hpp:571-611): out[n][k] = (1/T)^n d^n alphar/d(1/T)^n, n = 0..nmax (nmax 0..4) */
+int get_Arn0_batch(const long long int uuid, const int nmax, const long long int npts, const double* T, const double* rho,
+                   const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+/* AbstractModel::get_Arxy for several (NT[p], ND[p]) at once (teqpcpp.hpp:104-109; derivs.hpp:150-238): out[p][k] */
+int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, const int* ND, const long long int npts,
+                   const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out,
+                   const int flags, char* errmsg, int errmsg_length);
+/* every get_ATrhoXi combination in one call (derivs.hpp:247-292): out[((i*3+NT)*3+ND)*4+NXi][k], NT,ND in 0..2, NXi in 0..3 */
+int get_ATrhoXi_table_batch(const long long int uuid, const long long int npts, const double* T, const double* rho,
+                            const double* molefrac, const int Ncomp, double* out, const int flags,
+                            char* errmsg, int errmsg_length);
+/* IsochoricDerivatives::build_Psir_fgradHessian_autodiff (derivs.hpp:1051-1069): f[k], g[i][k], H[i*Ncomp+j][k]; any of f,g,H may be NULL */
+int build_Psir_fgradHessian_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                  const int Ncomp, double* f, double* g, double* H, const int flags,
+                                  char* errmsg, int errmsg_length);
+/* IsochoricDerivatives::get_ln_fugacity_coefficients / get_fugacity_coefficients (derivs.hpp:1208-1230): out[i][k] */
+int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                       const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+int get_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                    const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+
+/* ---------------- utilities ---------------- */
+int teqpb200_get_R(const long long int uuid, const double* molefrac, const int Ncomp, double* R, char* errmsg, int errmsg_length); /* AbstractModel::get_R, teqpcpp.hpp:102 */
+int teqpb200_get_ncomp(const long long int uuid, int* Ncomp, char* errmsg, int errmsg_length);
+int teqpb200_device_count(void);
+int teqpb200_set_devices(const int* device_ids, const int n, char* errmsg, int errmsg_length); /* host-pointer calls shard over these devices */
+int teqpb200_set_stream(void* cuda_stream);                 /* stream for TEQPB200_DEVICE_PTRS calls made by this thread */
+void* teqpb200_host_alloc(unsigned long long nbytes);       /* pinned host memory */
+void teqpb200_host_free(void* p);
+long long int teqpb200_kernel_launches(void);               /* kernels launched by this library so far (all threads) */
+/* deterministic synthetic state points on the device: counter-hash uniforms u_j(k) of the global point
+   index k0+k; T = Tlo + (Thi-Tlo) u0, rho log-uniform in [rholo, rhohi] from u1, x_i ~ z0_i exp(0.2 (2 u_{2+i} - 1)) renormalised.
+   Device pointers on the current device; rows of x have stride npts. */
+int teqpb200_synth_points(const long long int npts, const long long int k0, const unsigned long long seed, const double Tlo,
+                          const double Thi, const double rholo, const double rhohi, const double* z0_host, const int Ncomp,
+                          double* T, double* rho, double* x, char* errmsg, int errmsg_length);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,468 @@
+// C ABI of libteqpb200 (declared in include/teqpb200.h): the reference's extern "C" interface
+// (/root/reference/interface/C/teqpc.cpp:41-225) re-implemented over the GPU kernels, plus the batched entry points and the
+// host-side driver that shards a host-resident batch over the configured devices and streams it through each of them.
+#include <array>
+#include <atomic>
+#include <cstring>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <unordered_map>
+
+#include "../../include/teqpb200.h"
+#include "tq_common.hpp"
+
+namespace tq {
+
+int sm_count() {
+    static int cache[64] = {0};
+    int dev = 0;
+    TQ_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && cache[dev]) return cache[dev];
+    int n = 0;
+    TQ_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    if (dev < 64) cache[dev] = n;
+    return n;
+}
+
+std::unique_ptr<Model> make_model(const Json& j) {
+    // kind -> factory; the in-scope subset of /root/reference/interface/CPP/teqp_impl_factory.cpp:54-102
+    const std::string kind = j.at("kind").as_string();
+    const Json& spec = j.at("model");
+    if (kind == "vdW1" || kind == "vdW") return make_vdw_model(kind, spec);
+    if (kind == "PR" || kind == "SRK" || kind == "cubic") return make_cubic_model(kind, spec);
+    if (kind == "GERG2008resid" || kind == "GERG2004resid") return make_gerg_model(kind, spec);
+    if (kind == "PCSAFT") return make_pcsaft_model(spec);
+    throw InvalidArgument("Don't understand \"kind\" of: " + kind);
+}
+
+}  // namespace tq
+
+using namespace tq;
+
+namespace {
+
+std::mutex g_lib_mtx;
+std::unordered_map<long long, std::shared_ptr<Model>> g_library;
+std::atomic<long long> g_next_index{0};
+std::atomic<long long> g_launches{0};
+std::mutex g_dev_mtx;
+std::vector<int> g_devices;  // empty: the calling thread's current device
+thread_local cudaStream_t tl_stream = nullptr;
+
+struct CodeError : std::exception {  // the reference's teqpcException (teqpc.cpp:33-39)
+    int code; std::string msg;
+    CodeError(int c, std::string m) : code(c), msg(std::move(m)) {}
+    const char* what() const noexcept override { return msg.c_str(); }
+};
+
+void write_error(const std::string& msg, char* buf, int len) {
+    // same truncation rules as exception_handler in teqpc.cpp:45-73
+    if (!buf || len <= 0) return;
+    if (msg.size() < (size_t)len) { std::strcpy(buf, msg.c_str()); return; }
+    const std::string toolong = "Error message too long for buffer";
+    if (toolong.size() < (size_t)len) std::strcpy(buf, toolong.c_str());
+    else if (len > 1) std::strcpy(buf, "?");
+}
+
+// reference entry points collapse every std::exception to 9999; the new batched ones keep the numeric teqp code
+template<class F> int guarded(bool legacy, char* errmsg, int len, F&& f) {
+    try { f(); return 0; }
+    catch (const CodeError& e) { write_error(e.msg, errmsg, len); return e.code; }
+    catch (const Error& e) { write_error(e.msg, errmsg, len); return legacy ? 9999 : e.code; }
+    catch (const std::exception& e) { write_error(e.what(), errmsg, len); return 9999; }
+    catch (...) { write_error("unknown error", errmsg, len); return 9999; }
+}
+
+std::shared_ptr<Model> lookup(long long uuid) {
+    std::lock_guard<std::mutex> g(g_lib_mtx);
+    auto it = g_library.find(uuid);
+    if (it == g_library.end()) throw std::out_of_range("unordered_map::at");  // what .at() does in the reference (teqpc.cpp:111)
+    return it->second;
+}
+
+void check_ncomp(const Model& m, int Ncomp) {
+    if (Ncomp != m.ncomp()) throw InvalidArgument("mole fractions must be of size " + std::to_string(m.ncomp()) + " but are of size " + std::to_string(Ncomp));
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host-resident batches: shard over devices, stream through each device in chunks
+// ---------------------------------------------------------------------------------------------------------------------
+struct HostIn { const double* p; int rows; bool broadcast; };
+struct HostOut { double* p; int rows; };  // p == nullptr: device-only scratch rows
+using ChunkFn = std::function<void(long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st)>;
+
+constexpr int kSlots = 3;
+constexpr long long kMaxChunk = 1LL << 22;
+constexpr long long kMinChunk = 1LL << 16;
+
+struct DeviceArena {  // grow-only device scratch, one per (device, slot)
+    double* p = nullptr; size_t cap = 0; cudaStream_t st = nullptr;
+};
+std::mutex g_run_mtx;
+std::unordered_map<int, std::array<DeviceArena, kSlots>> g_arenas;
+
+void run_on_device(int dev, long long k0, long long n_dev, long long npts, const std::vector<HostIn>& ins,
+                   const std::vector<HostOut>& outs, const ChunkFn& fn) {
+    if (n_dev <= 0) return;
+    TQ_CUDA(cudaSetDevice(dev));
+    auto& arenas = g_arenas[dev];
+    long long chunk = std::min(kMaxChunk, std::max(kMinChunk, (n_dev + 7) / 8));
+    chunk = std::min(chunk, n_dev);
+    size_t rows_total = 0;
+    for (auto& a : ins) rows_total += a.rows;
+    for (auto& a : outs) rows_total += a.rows;
+    const size_t need = rows_total * (size_t)chunk * sizeof(double);
+    for (int s = 0; s < kSlots; ++s) {
+        DeviceArena& A = arenas[s];
+        if (!A.st) TQ_CUDA(cudaStreamCreateWithFlags(&A.st, cudaStreamNonBlocking));
+        if (A.cap < need) {
+            if (A.p) { TQ_CUDA(cudaStreamSynchronize(A.st)); TQ_CUDA(cudaFree(A.p)); A.p = nullptr; A.cap = 0; }
+            TQ_CUDA(cudaMalloc(&A.p, need));
+            A.cap = need;
+        }
+    }
+    int slot = 0;
+    for (long long c0 = 0; c0 < n_dev; c0 += chunk, slot = (slot + 1) % kSlots) {
+        const long long n = std::min(chunk, n_dev - c0);
+        DeviceArena& A = arenas[slot];
+        cudaStream_t st = A.st;
+        double* cur = A.p;
+        std::vector<const double*> din; std::vector<double*> dout;
+        for (auto& a : ins) {
+            din.push_back(cur);
+            if (a.broadcast) {
+                TQ_CUDA(cudaMemcpyAsync(cur, a.p, sizeof(double) * a.rows, cudaMemcpyHostToDevice, st));
+            } else {
+                TQ_CUDA(cudaMemcpy2DAsync(cur, sizeof(double) * n, a.p + k0 + c0, sizeof(double) * npts, sizeof(double) * n, a.rows, cudaMemcpyHostToDevice, st));
+            }
+            cur += (size_t)a.rows * chunk;
+        }
+        for (auto& a : outs) { dout.push_back(cur); cur += (size_t)a.rows * chunk; }
+        fn(n, din, dout, st);
+        for (size_t q = 0; q < outs.size(); ++q) {
+            if (!outs[q].p) continue;
+            TQ_CUDA(cudaMemcpy2DAsync(outs[q].p + k0 + c0, sizeof(double) * npts, dout[q], sizeof(double) * n, sizeof(double) * n, outs[q].rows, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    for (int s = 0; s < kSlots; ++s) TQ_CUDA(cudaStreamSynchronize(arenas[s].st));
+}
+
+void run_host(long long npts, const std::vector<HostIn>& ins, const std::vector<HostOut>& outs, const ChunkFn& fn) {
+    if (npts <= 0) return;
+    std::lock_guard<std::mutex> g(g_run_mtx);
+    std::vector<int> devs;
+    { std::lock_guard<std::mutex> gd(g_dev_mtx); devs = g_devices; }
+    int cur = 0;
+    TQ_CUDA(cudaGetDevice(&cur));
+    if (devs.empty() || npts < (long long)devs.size() * 1024) devs = {devs.empty() ? cur : devs[0]};
+    const int nd = (int)devs.size();
+    for (int d : devs) (void)g_arenas[d];  // create the map entries before any worker thread touches the map
+    if (nd == 1) { run_on_device(devs[0], 0, npts, npts, ins, outs, fn); TQ_CUDA(cudaSetDevice(cur)); return; }
+    // contiguous even split, remainder to the last device; one host thread per device
+    const long long per = npts / nd;
+    std::vector<std::thread> th;
+    std::vector<std::string> errs(nd);
+    std::vector<int> codes(nd, 0);
+    for (int d = 0; d < nd; ++d) {
+        const long long k0 = per * d, n = (d == nd - 1) ? npts - k0 : per;
+        th.emplace_back([&, d, k0, n] {
+            try { run_on_device(devs[d], k0, n, npts, ins, outs, fn); }
+            catch (const Error& e) { codes[d] = e.code; errs[d] = e.msg; }
+            catch (const std::exception& e) { codes[d] = 9999; errs[d] = e.what(); }
+        });
+    }
+    for (auto& t : th) t.join();
+    TQ_CUDA(cudaSetDevice(cur));
+    for (int d = 0; d < nd; ++d) if (codes[d]) throw Error(codes[d], errs[d]);
+}
+
+// one entry point for both pointer kinds
+void run(int flags, long long npts, const std::vector<HostIn>& ins, const std::vector<HostOut>& outs, const ChunkFn& fn) {
+    if (npts < 0) throw InvalidArgument("npts must be non-negative");
+    if (npts == 0) return;
+    if (flags & TEQPB200_DEVICE_PTRS) {
+        std::vector<const double*> din; std::vector<double*> dout;
+        std::vector<double*> scratch;
+        for (auto& a : ins) din.push_back(a.p);
+        for (auto& a : outs) {
+            if (a.p) { dout.push_back(a.p); continue; }
+            double* s = nullptr;
+            TQ_CUDA(cudaMallocAsync(&s, sizeof(double) * (size_t)a.rows * npts, tl_stream));
+            scratch.push_back(s); dout.push_back(s);
+        }
+        fn(npts, din, dout, tl_stream);
+        for (double* s : scratch) TQ_CUDA(cudaFreeAsync(s, tl_stream));
+    } else {
+        run_host(npts, ins, outs, fn);
+    }
+}
+
+DeviceBatch make_batch(long long n, const double* T, const double* rho, const double* x, bool broadcast) {
+    DeviceBatch b;
+    b.npts = n; b.T = T; b.rho = rho; b.x = x; b.x_stride = broadcast ? 0 : n;
+    return b;
+}
+
+void ar_table_call(const Model& m, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, int Ncomp,
+                   double* out, int flags) {
+    check_ncomp(m, Ncomp);
+    const bool bc = flags & TEQPB200_BROADCAST_X;
+    run(flags, npts, {{T, 1, false}, {rho, 1, false}, {x, Ncomp, bc}}, {{out, (NT + 1) * (ND + 1)}},
+        [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+            m.launch_ar_table(NT, ND, make_batch(n, din[0], din[1], din[2], bc), dout[0], st);
+            ++g_launches;
+        });
+}
+
+}  // namespace
+
+extern "C" {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Part 1: reference ABI
+// ---------------------------------------------------------------------------------------------------------------------
+int build_model(const char* j, long long int* uuid, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        Json json = Json::parse(j);
+        const long long uid = g_next_index++;
+        std::shared_ptr<Model> m;
+        try { m = tq::make_model(json); }
+        catch (const std::exception& e) { throw CodeError(30, "Unable to load with error:" + std::string(e.what())); }
+        { std::lock_guard<std::mutex> g(g_lib_mtx); g_library.emplace(uid, std::move(m)); }
+        *uuid = uid;
+    });
+}
+
+int free_model(const long long int uuid, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] { std::lock_guard<std::mutex> g(g_lib_mtx); g_library.erase(uuid); });
+}
+
+int get_Arxy(const long long int uuid, const int NT, const int ND, const double T, const double rho, const double* molefrac,
+             const int Ncomp, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        // runtime dispatch of the reference accepts only these (derivs.hpp:627-682)
+        if (NT < 0 || ND < 0 || NT + ND > 3) throw std::invalid_argument("Not valid: NT=" + std::to_string(NT) + ", ND=" + std::to_string(ND));
+        std::vector<double> table((NT + 1) * (ND + 1));
+        ar_table_call(*m, NT, ND, 1, &T, &rho, molefrac, Ncomp, table.data(), 0);
+        *val = table[NT * (ND + 1) + ND];
+    });
+}
+
+int get_ATrhoXi(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND, const double* molefrac,
+                const int Ncomp, const int i, const int NXi, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        // combinations the reference compiles (derivs.hpp:261-284): NT+ND <= 2, NXi <= 3, not all zero
+        if (NT < 0 || ND < 0 || NXi < 0 || NT + ND > 2 || NXi > 3 || (NT + ND + NXi) == 0) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp) throw std::invalid_argument("component index out of range");
+        std::vector<double> table((size_t)Ncomp * 36);
+        run(0, 1, {{&T, 1, false}, {&rhomolar, 1, false}, {molefrac, Ncomp, false}}, {{table.data(), Ncomp * 36}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXi_table(make_batch(n, din[0], din[1], din[2], false), dout[0], st);
+                ++g_launches;
+            });
+        *val = table[((i * 3 + NT) * 3 + ND) * 4 + NXi];
+    });
+}
+
+#define TQ_NOT_YET(name)                                                                                              \
+    return guarded(true, errmsg, errmsg_length, [&] {                                                                 \
+        (void)lookup(uuid);                                                                                           \
+        throw NotImplementedError(name " is not implemented in libteqpb200 yet");                                    \
+    })
+
+int get_ATrhoXiXj(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
+                  const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_ATrhoXiXj"); }
+int get_ATrhoXiXjXk(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
+                    const int, const int, const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_ATrhoXiXjXk"); }
+int get_AtaudeltaXi(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
+                    const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXi"); }
+int get_AtaudeltaXiXj(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
+                      const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXj"); }
+int get_AtaudeltaXiXjXk(const long long int uuid, const double, const int, const double, const int, const double*, const int,
+                        const int, const int, const int, const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXjXk"); }
+int get_dmBnvirdTm(const long long int uuid, const int, const int, const double, const double*, const int, double*, char* errmsg,
+                   int errmsg_length) { TQ_NOT_YET("get_dmBnvirdTm"); }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Part 2: batched
+// ---------------------------------------------------------------------------------------------------------------------
+int get_Ar0n_batch(const long long int uuid, const int nmax, const long long int npts, const double* T, const double* rho,
+                   const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        if (nmax < 0 || nmax > kMaxDerivD) throw InvalidArgument("nmax must be 0..6");
+        ar_table_call(*m, 0, nmax, npts, T, rho, molefrac, Ncomp, out, flags);
+    });
+}
+
+int get_Arn0_batch(const long long int uuid, const int nmax, const long long int npts, const double* T, const double* rho,
+                   const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        if (nmax < 0 || nmax > kMaxDerivT) throw InvalidArgument("nmax must be 0..4");
+        ar_table_call(*m, nmax, 0, npts, T, rho, molefrac, Ncomp, out, flags);
+    });
+}
+
+int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, const int* ND, const long long int npts,
+                   const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out, const int flags,
+                   char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (npairs <= 0) throw InvalidArgument("npairs must be positive");
+        int NTm = 0, NDm = 0;
+        for (int p = 0; p < npairs; ++p) {
+            if (NT[p] < 0 || ND[p] < 0 || NT[p] > kMaxDerivT || ND[p] > kMaxDerivD) throw InvalidArgument("derivative order out of range");
+            NTm = std::max(NTm, NT[p]); NDm = std::max(NDm, ND[p]);
+        }
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        const int rows = (NTm + 1) * (NDm + 1);
+        // one sweep computes the covering table; the requested rows are then gathered
+        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, npairs}, {nullptr, rows}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ar_table(NTm, NDm, make_batch(n, din[0], din[1], din[2], bc), dout[1], st);
+                ++g_launches;
+                for (int p = 0; p < npairs; ++p)
+                    TQ_CUDA(cudaMemcpyAsync(dout[0] + (size_t)p * n, dout[1] + (size_t)(NT[p] * (NDm + 1) + ND[p]) * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+            });
+    });
+}
+
+int get_ATrhoXi_table_batch(const long long int uuid, const long long int npts, const double* T, const double* rho,
+                            const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, Ncomp * 36}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXi_table(make_batch(n, din[0], din[1], din[2], bc), dout[0], st);
+                ++g_launches;
+            });
+    });
+}
+
+static void isochoric_call(const Model& m, long long npts, const double* T, const double* rhovec, int Ncomp, double* f, double* g,
+                           double* H, double* lnphi, double* phi, int flags) {
+    check_ncomp(m, Ncomp);
+    if (flags & TEQPB200_BROADCAST_X) throw InvalidArgument("TEQPB200_BROADCAST_X does not apply to rhovec inputs");
+    std::vector<HostOut> outs;
+    std::vector<int> slot(5, -1);
+    auto add = [&](double* p, int rows, int which) { if (p) { slot[which] = (int)outs.size(); outs.push_back({p, rows}); } };
+    add(f, 1, 0); add(g, Ncomp, 1); add(H, Ncomp * Ncomp, 2); add(lnphi, Ncomp, 3); add(phi, Ncomp, 4);
+    if (outs.empty()) return;
+    run(flags, npts, {{T, 1, false}, {rhovec, Ncomp, false}}, outs,
+        [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+            IsochoricOut o;
+            if (slot[0] >= 0) o.Psir = dout[slot[0]];
+            if (slot[1] >= 0) o.grad = dout[slot[1]];
+            if (slot[2] >= 0) o.hess = dout[slot[2]];
+            if (slot[3] >= 0) o.lnphi = dout[slot[3]];
+            if (slot[4] >= 0) o.phi = dout[slot[4]];
+            m.launch_isochoric(make_batch(n, din[0], nullptr, din[1], false), o, st);
+            ++g_launches;
+        });
+}
+
+int build_Psir_fgradHessian_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                  const int Ncomp, double* f, double* g, double* H, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, f, g, H, nullptr, nullptr, flags); });
+}
+int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                       const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, nullptr, nullptr, nullptr, out, nullptr, flags); });
+}
+int get_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
+                                    const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, nullptr, nullptr, nullptr, nullptr, out, flags); });
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// utilities
+// ---------------------------------------------------------------------------------------------------------------------
+int teqpb200_get_R(const long long int uuid, const double* molefrac, const int Ncomp, double* R, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { auto m = lookup(uuid); check_ncomp(*m, Ncomp); *R = m->R(molefrac, Ncomp); });
+}
+int teqpb200_get_ncomp(const long long int uuid, int* Ncomp, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { *Ncomp = lookup(uuid)->ncomp(); });
+}
+int teqpb200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+int teqpb200_set_devices(const int* device_ids, const int n, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        const int have = teqpb200_device_count();
+        std::vector<int> d;
+        for (int i = 0; i < n; ++i) {
+            if (device_ids[i] < 0 || device_ids[i] >= have) throw InvalidArgument("no such CUDA device: " + std::to_string(device_ids[i]));
+            d.push_back(device_ids[i]);
+        }
+        std::lock_guard<std::mutex> g(g_dev_mtx);
+        g_devices = d;
+    });
+}
+int teqpb200_set_stream(void* cuda_stream) { tl_stream = static_cast<cudaStream_t>(cuda_stream); return 0; }
+void* teqpb200_host_alloc(unsigned long long nbytes) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, nbytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+void teqpb200_host_free(void* p) { if (p) cudaFreeHost(p); }
+long long int teqpb200_kernel_launches(void) { return g_launches.load(); }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// synthetic state points
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+__device__ __forceinline__ double u01(unsigned long long seed, unsigned long long k, unsigned long long j) {
+    unsigned long long z = seed ^ (k * 0x9E3779B97F4A7C15ULL + j);
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z = z ^ (z >> 31);
+    return (double)(z >> 11) * (1.0 / 9007199254740992.0);
+}
+constexpr int kSynthMaxC = 32;
+struct SynthParams { double z0[kSynthMaxC]; };
+__global__ void synth_kernel(const __grid_constant__ SynthParams sp, long long npts, long long k0, unsigned long long seed, double Tlo, double Thi,
+                             double lnlo, double lnhi, int nc, double* T, double* rho, double* x) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        const unsigned long long gk = (unsigned long long)(k0 + k);
+        T[k] = Tlo + (Thi - Tlo) * u01(seed, gk, 0);
+        rho[k] = exp(lnlo + (lnhi - lnlo) * u01(seed, gk, 1));
+        double s = 0.0;
+        for (int i = 0; i < nc; ++i) {
+            const double v = sp.z0[i] * exp(0.2 * (2.0 * u01(seed, gk, 2 + i) - 1.0));
+            x[(long long)i * npts + k] = v;
+            s += v;
+        }
+        for (int i = 0; i < nc; ++i) x[(long long)i * npts + k] /= s;
+    }
+}
+}  // namespace
+
+extern "C" int teqpb200_synth_points(const long long int npts, const long long int k0, const unsigned long long seed, const double Tlo,
+                                     const double Thi, const double rholo, const double rhohi, const double* z0_host, const int Ncomp,
+                                     double* T, double* rho, double* x, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        if (Ncomp < 1 || Ncomp > kSynthMaxC) throw InvalidArgument("Ncomp out of range for the synthetic generator");
+        if (npts <= 0) return;
+        SynthParams sp{};
+        for (int i = 0; i < Ncomp; ++i) sp.z0[i] = z0_host[i];
+        const int block = 256;
+        const int grid = grid_for(npts, block, sm_count() * 8);
+        synth_kernel<<<grid, block, 0, tl_stream>>>(sp, npts, k0, seed, Tlo, Thi, std::log(rholo), std::log(rhohi), Ncomp, T, rho, x);
+        TQ_CUDA(cudaGetLastError());
+        ++g_launches;
+    });
+}

@@ -1,0 +1,274 @@
+// Generic jet-sweep kernels, shared by every model family whose alphar(T, rho, x) is written once over jet types
+// (cubic, PC-SAFT, SAFT-VR-Mie, ...).  A family supplies
+//
+//   struct Dev { using Params = <POD>;                                   // passed as a __grid_constant__ kernel parameter
+//                template<int MAXN, class TT, class RT, class XT>
+//                static __device__ auto alphar(const Params&, const TT& T, const RT& rho, const XT* x);
+//                template<class XT> static __device__ auto R(const Params&, const XT* x); };
+//
+// and gets, one state point per thread:
+//   * generic_launch_ar_table   -- Lambda^r_nm for all n<=NT, m<=ND in ONE sweep of a J3<NT,ND,0> jet
+//                                  (reference: one nested-dual sweep per (n,m), derivs.hpp:150-238, 543-624)
+//   * generic_launch_ATrhoXi    -- the whole get_ATrhoXi table per component in one J3<2,2,3> sweep (derivs.hpp:247-292)
+//   * generic_launch_isochoric  -- Psi^r, its gradient and Hessian in the molar concentrations and ln(phi)
+//                                  (derivs.hpp:1031-1124, 1208-1230)
+#pragma once
+#include "tq_common.hpp"
+#include "tq_jet.cuh"
+
+namespace tq {
+
+// ------------------------------------------------------------------------------------------------------------------
+// Lambda^r_nm table
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN, int CT, int CD>
+TQ_HD void generic_ar_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin,
+                            const int NT, const int ND, double* out, const long long ostride) {
+    using XT = J3<0, 0, 0>;
+    XT x[MAXN];
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+    for (int i = 0; i < MAXN; ++i)
+        if (i < nc) x[i] = XT(xin[i]);
+    using TT = J3<CT, 0, 0>;
+    using RT = J3<0, CD, 0>;
+    const TT T = TT::reciprocal_scaled_variable(T0);
+    RT rho;
+    rho.c[0] = Tay<CD, Tay<0, double>>::scaled_variable(rho0);
+    const J3<CT, CD, 0> a = embed<J3<CT, CD, 0>>(M::template alphar<MAXN>(p, T, rho, x));
+    double fn = 1.0;
+#pragma unroll
+    for (int n = 0; n <= CT; ++n) {
+        if (n >= 2) fn *= double(n);
+        double fm = 1.0;
+#pragma unroll
+        for (int m = 0; m <= CD; ++m) {
+            if (m >= 2) fm *= double(m);
+            if (n <= NT && m <= ND) out[(long long)(n * (ND + 1) + m) * ostride] = (fn * fm) * a.c[n].c[m].c[0];
+        }
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int MAXN>
+__device__ __forceinline__ void load_x(double (&x)[MAXN], const int nc, const DeviceBatch& in, const long long k) {
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+    for (int i = 0; i < MAXN; ++i)
+        if (i < nc) x[i] = __ldg(in.x + (long long)i * in.x_stride + (in.x_stride ? k : 0));
+}
+
+template<class M, int MAXN, int CT, int CD>
+__global__ void __launch_bounds__(128) generic_ar_table_kernel(const __grid_constant__ typename M::Params p, const int nc,
+                                                               const DeviceBatch in, const int NT, const int ND,
+                                                               double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double x[MAXN];
+        load_x<M, MAXN>(x, nc, in, k);
+        generic_ar_point<M, MAXN, CT, CD>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, NT, ND, out + k, npts);
+    }
+}
+
+template<class M, int CT, int CD>
+void generic_launch_ar_table_inst(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
+    const int block = 128;
+    const int grid = grid_for(in.npts, block, sm_count() * 32);
+    if (nc == 1) generic_ar_table_kernel<M, 1, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    else if (nc == 2) generic_ar_table_kernel<M, 2, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    else if (nc == 3) generic_ar_table_kernel<M, 3, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    else generic_ar_table_kernel<M, M::kMaxC, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    TQ_CUDA(cudaGetLastError());
+}
+
+// picks the smallest compiled jet shape that covers (NT, ND)
+template<class M>
+void generic_launch_ar_table(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
+    if (NT < 0 || NT > kMaxDerivT || ND < 0 || ND > kMaxDerivD) throw InvalidArgument("derivative order out of range");
+    if (in.npts == 0) return;
+    if (NT == 0) {
+        if (ND <= 2) generic_launch_ar_table_inst<M, 0, 2>(p, nc, NT, ND, in, out, st);
+        else if (ND <= 4) generic_launch_ar_table_inst<M, 0, 4>(p, nc, NT, ND, in, out, st);
+        else generic_launch_ar_table_inst<M, 0, 6>(p, nc, NT, ND, in, out, st);
+    } else if (ND == 0) {
+        if (NT <= 2) generic_launch_ar_table_inst<M, 2, 0>(p, nc, NT, ND, in, out, st);
+        else generic_launch_ar_table_inst<M, 4, 0>(p, nc, NT, ND, in, out, st);
+    } else if (NT <= 2 && ND <= 2) {
+        generic_launch_ar_table_inst<M, 2, 2>(p, nc, NT, ND, in, out, st);
+    } else if (NT <= 2 && ND <= 4) {
+        generic_launch_ar_table_inst<M, 2, 4>(p, nc, NT, ND, in, out, st);
+    } else {
+        throw InvalidArgument("mixed derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is larger than the compiled jet shapes (NT<=2 with ND<=4, or one of them zero)");
+    }
+}
+
+#endif  // __CUDACC__
+
+// ------------------------------------------------------------------------------------------------------------------
+// get_ATrhoXi table: out[((i*3+nt)*3+nd)*4+nxi][npts], nt,nd in 0..2, nxi in 0..3
+// ------------------------------------------------------------------------------------------------------------------
+
+template<class M, int MAXN>
+TQ_HD void generic_ATrhoXi_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin,
+                                 double* out, const long long ostride) {
+    using XT = J3<0, 0, 3>;
+    using TT = J3<2, 0, 0>;
+    using RT = J3<0, 2, 0>;
+    const TT T = TT::reciprocal_scaled_variable(T0);
+    RT rho;
+    rho.c[0] = Tay<2, Tay<0, double>>::scaled_variable(rho0);
+    for (int i = 0; i < nc; ++i) {
+        XT x[MAXN];
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+        for (int j = 0; j < MAXN; ++j) {
+            if (j < nc) {
+                x[j] = XT(xin[j]);
+                if (j == i) x[j].c[0].c[0].c[1] = 1.0;
+            }
+        }
+        const J3<2, 2, 3> a = embed<J3<2, 2, 3>>(M::template alphar<MAXN>(p, T, rho, x));
+#pragma unroll
+        for (int nt = 0; nt <= 2; ++nt)
+#pragma unroll
+            for (int nd = 0; nd <= 2; ++nd)
+#pragma unroll
+                for (int nx = 0; nx <= 3; ++nx) {
+                    const double f = (nt == 2 ? 2.0 : 1.0) * (nd == 2 ? 2.0 : 1.0) * (nx == 2 ? 2.0 : (nx == 3 ? 6.0 : 1.0));
+                    out[(long long)(((i * 3 + nt) * 3 + nd) * 4 + nx) * ostride] = f * a.c[nt].c[nd].c[nx];
+                }
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int MAXN>
+__global__ void __launch_bounds__(64) generic_ATrhoXi_kernel(const __grid_constant__ typename M::Params p, const int nc,
+                                                             const DeviceBatch in, double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double x[MAXN];
+        load_x<M, MAXN>(x, nc, in, k);
+        generic_ATrhoXi_point<M, MAXN>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, out + k, npts);
+    }
+}
+
+template<class M>
+void generic_launch_ATrhoXi(const typename M::Params& p, int nc, const DeviceBatch& in, double* out, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    const int grid = grid_for(in.npts, block, sm_count() * 32);
+    if (nc == 1) generic_ATrhoXi_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, out);
+    else if (nc == 2) generic_ATrhoXi_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, out);
+    else if (nc == 3) generic_ATrhoXi_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, out);
+    else generic_ATrhoXi_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, out);
+    TQ_CUDA(cudaGetLastError());
+}
+
+#endif  // __CUDACC__
+
+// ------------------------------------------------------------------------------------------------------------------
+// Isochoric family.  in.x holds the molar concentrations rhovec[nc][npts]; in.rho is unused.
+// Psi^r(T, rhovec) = alphar(T, sum rhovec, rhovec / sum rhovec) * R(x) * T * sum rhovec      (derivs.hpp:1038-1042)
+// Levels: 1 = unit perturbation of rho_i, 2 = unit perturbation of rho_j.
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN, int B, int C>
+TQ_HD J3<0, B, C> psir_jet(const typename M::Params& p, int nc, double T0, const double* rv, int i, int j) {
+    using XT = J3<0, B, C>;
+    XT r[MAXN];
+    XT rhotot(0.0);
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+    for (int k = 0; k < MAXN; ++k) {
+        if (k < nc) {
+            r[k] = XT(rv[k]);
+            if (B >= 1 && k == i) r[k].c[0].c[B >= 1 ? 1 : 0].c[0] = 1.0;
+            if (C >= 1 && k == j) r[k].c[0].c[0].c[C >= 1 ? 1 : 0] = 1.0;
+            rhotot = rhotot + r[k];
+        }
+    }
+    const XT inv = trecip(rhotot);
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+    for (int k = 0; k < MAXN; ++k)
+        if (k < nc) r[k] = r[k] * inv;  // mole fractions
+    const J3<0, 0, 0> T(T0);
+    const XT a = embed<XT>(M::template alphar<MAXN>(p, T, rhotot, r));
+    return a * M::R(p, r) * T0 * rhotot;
+}
+
+template<class M, int MAXN>
+TQ_HD void generic_isochoric_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const IsochoricOut& o,
+                                   const long long k, const long long npts) {
+    double rhotot = 0.0;
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+    for (int i = 0; i < MAXN; ++i)
+        if (i < nc) rhotot += rv[i];
+    const bool want_h = o.hess != nullptr;
+    double lnZ = 0.0, RT = 0.0;
+    if (o.lnphi || o.phi) {
+        // Z = 1 + Lambda_01 at x = rhovec/rhotot (derivs.hpp:1221-1225)
+        using XT0 = J3<0, 0, 0>;
+        XT0 x[MAXN];
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+        for (int i = 0; i < MAXN; ++i)
+            if (i < nc) x[i] = XT0(rv[i] / rhotot);
+        J3<0, 1, 0> rho;
+        rho.c[0] = Tay<1, Tay<0, double>>::scaled_variable(rhotot);
+        const J3<0, 1, 0> a = embed<J3<0, 1, 0>>(M::template alphar<MAXN>(p, XT0(T0), rho, x));
+        lnZ = log(1.0 + a.c[0].c[1].c[0]);
+        RT = base(M::R(p, x)) * T0;
+    }
+    for (int i = 0; i < nc; ++i) {
+        if (want_h) {
+            const J3<0, 2, 0> d = psir_jet<M, MAXN, 2, 0>(p, nc, T0, rv, i, -1);
+            const double g = d.c[0].c[1].c[0];
+            if (i == 0 && o.Psir) o.Psir[k] = d.c[0].c[0].c[0];
+            if (o.grad) o.grad[(long long)i * npts + k] = g;
+            if (o.lnphi) o.lnphi[(long long)i * npts + k] = g / RT - lnZ;
+            if (o.phi) o.phi[(long long)i * npts + k] = exp(g / RT - lnZ);
+            o.hess[(long long)(i * nc + i) * npts + k] = 2.0 * d.c[0].c[2].c[0];
+            for (int j = i + 1; j < nc; ++j) {
+                const J3<0, 1, 1> e = psir_jet<M, MAXN, 1, 1>(p, nc, T0, rv, i, j);
+                const double h = e.c[0].c[1].c[1];
+                o.hess[(long long)(i * nc + j) * npts + k] = h;
+                o.hess[(long long)(j * nc + i) * npts + k] = h;
+            }
+        } else {
+            const J3<0, 1, 0> d = psir_jet<M, MAXN, 1, 0>(p, nc, T0, rv, i, -1);
+            const double g = d.c[0].c[1].c[0];
+            if (i == 0 && o.Psir) o.Psir[k] = d.c[0].c[0].c[0];
+            if (o.grad) o.grad[(long long)i * npts + k] = g;
+            if (o.lnphi) o.lnphi[(long long)i * npts + k] = g / RT - lnZ;
+            if (o.phi) o.phi[(long long)i * npts + k] = exp(g / RT - lnZ);
+        }
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int MAXN>
+__global__ void __launch_bounds__(64) generic_isochoric_kernel(const __grid_constant__ typename M::Params p, const int nc,
+                                                               const DeviceBatch in, const IsochoricOut o) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double rv[MAXN];
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+        for (int i = 0; i < MAXN; ++i)
+            if (i < nc) rv[i] = __ldg(in.x + (long long)i * in.x_stride + k);
+        generic_isochoric_point<M, MAXN>(p, nc, __ldg(in.T + k), rv, o, k, npts);
+    }
+}
+
+template<class M>
+void generic_launch_isochoric(const typename M::Params& p, int nc, const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    const int grid = grid_for(in.npts, block, sm_count() * 32);
+    if (nc == 1) generic_isochoric_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, o);
+    else if (nc == 2) generic_isochoric_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, o);
+    else if (nc == 3) generic_isochoric_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, o);
+    else generic_isochoric_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, o);
+    TQ_CUDA(cudaGetLastError());
+}
+
+
+#endif  // __CUDACC__
+
+}  // namespace tq

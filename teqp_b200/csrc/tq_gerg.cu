@@ -1,0 +1,220 @@
+// GERG-2004/2008 residual models: names -> term program (host) and the batched Lambda^r_nm kernel (device).
+// See tq_gerg.cuh for the factorisation.  Reference factories: /root/reference/interface/CPP/model_factory_GERG.cpp:13-18,
+// model classes /root/reference/include/teqp/models/GERG/GERG.hpp:902-937 (2004) and :1166-1202 (2008).
+#include <algorithm>
+#include <cctype>
+#include <map>
+#include <tuple>
+
+#include "tq_common.hpp"
+#include "tq_gerg.cuh"
+
+namespace tq {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------------------------------
+// published coefficient tables (generated, see tools/dump_gerg_tables.cpp)
+// ---------------------------------------------------------------------------------------------------------------------
+struct GergFluid {
+    const char* name;
+    double rhoc_molm3, Tc_K, M_kgmol;
+    std::vector<double> n, t, d, c, l;
+};
+struct GergPair {
+    size_t i, j;
+    double betaV, gammaV, betaT, gammaT, Fij;
+    std::vector<double> n, t, d, eta, beta, gamma, epsilon;
+};
+#include "data/gerg_tables.inc"
+
+constexpr int kBlock = 128;
+
+// ---------------------------------------------------------------------------------------------------------------------
+// device
+// ---------------------------------------------------------------------------------------------------------------------
+template<int NT, int ND>
+__global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_constant__ GergProgram P, const DeviceBatch in,
+                                                               double* __restrict__ out) {
+    extern __shared__ double Wsh[];  // [nw][kBlock]; each thread touches only its own column -> no barriers needed
+    double* W = Wsh + threadIdx.x;
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * kBlock;
+    for (long long k = (long long)blockIdx.x * kBlock + threadIdx.x; k < npts; k += stride) {
+        const double T = __ldg(in.T + k);
+        const double rho = __ldg(in.rho + k);
+        for (int i = 0; i < P.nc; ++i) W[i * kBlock] = __ldg(in.x + (long long)i * in.x_stride + (in.x_stride ? k : 0));
+        double A[NT + 1][ND + 1];
+        gerg_point<NT, ND>(P, T, rho, W, kBlock, A);
+        double fn = 1.0;
+#pragma unroll
+        for (int n = 0; n <= NT; ++n) {
+            if (n >= 2) fn *= double(n);
+            double fm = 1.0;
+#pragma unroll
+            for (int m = 0; m <= ND; ++m) {
+                if (m >= 2) fm *= double(m);
+                out[(long long)(n * (ND + 1) + m) * npts + k] = (fn * fm) * A[n][m];
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host: names -> program
+// ---------------------------------------------------------------------------------------------------------------------
+std::string lower(std::string s) {
+    for (auto& ch : s) ch = (char)std::tolower((unsigned char)ch);
+    return s;
+}
+double binom_real(double a, int m) {
+    double r = 1.0;
+    for (int k = 1; k <= m; ++k) r = r * (a - (k - 1)) / k;
+    return r;
+}
+
+struct RawTerm {
+    int w;       // weight index
+    double n, t;
+    int kind, d, l;
+    double c, eta, eps, beta, gamma;
+};
+
+class GergModel final : public Model {
+public:
+    GergProgram P{};
+    std::vector<std::string> names;
+    double Rgas = 8.314472;  // GERG.hpp:1175 (2008), :906 (2004)
+    std::string fam;
+    int ncomp() const override { return P.nc; }
+    const char* family() const override { return fam.c_str(); }
+    double R(const double*, int) const override { return Rgas; }
+    const void* params_blob(size_t* n) const override { *n = sizeof(P); return &P; }
+
+    template<int NT, int ND> void launch(const DeviceBatch& in, double* out, cudaStream_t st) const {
+        const size_t smem = (size_t)P.nw * kBlock * sizeof(double);
+        static_assert(kGergMaxW * kBlock * sizeof(double) <= 48 * 1024, "W staging must fit the default 48 KB dynamic shared memory");
+        const int grid = grid_for(in.npts, kBlock, sm_count() * 8);
+        gerg_ar_table_kernel<NT, ND><<<grid, kBlock, smem, st>>>(P, in, out);
+        TQ_CUDA(cudaGetLastError());
+    }
+    // the compiled shapes; out is laid out for the REQUESTED (NT, ND), so a wider kernel writes through a scratch-free
+    // remap only when shapes match exactly -- otherwise the caller (capi) asks for a compiled shape and slices.
+    void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override {
+        if (in.npts == 0) return;
+#define TQ_CASE(a, b) if (NT == a && ND == b) { launch<a, b>(in, out, st); return; }
+        TQ_CASE(0, 0) TQ_CASE(0, 1) TQ_CASE(0, 2) TQ_CASE(0, 3) TQ_CASE(0, 4) TQ_CASE(0, 5) TQ_CASE(0, 6)
+        TQ_CASE(1, 0) TQ_CASE(2, 0) TQ_CASE(3, 0) TQ_CASE(4, 0)
+        TQ_CASE(1, 1) TQ_CASE(1, 2) TQ_CASE(2, 1) TQ_CASE(2, 2) TQ_CASE(1, 3) TQ_CASE(1, 4) TQ_CASE(2, 3) TQ_CASE(2, 4)
+#undef TQ_CASE
+        throw InvalidArgument("derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is not a compiled shape for " + fam);
+    }
+};
+
+template<class F, class PR>
+std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string>& names_in, const F* fluids, size_t nfluids, const PR* pairs, size_t npairs) {
+    auto m = std::make_unique<GergModel>();
+    m->fam = fam;
+    GergProgram& P = m->P;
+    const size_t N = names_in.size();
+    if (N == 0) throw InvalidArgument("names must not be empty");
+    if (N > (size_t)kGergMaxC) throw InvalidArgument("too many components");
+    std::vector<size_t> idx(N);
+    for (size_t i = 0; i < N; ++i) {
+        const std::string nm = lower(names_in[i]);
+        size_t f = nfluids;
+        for (size_t q = 0; q < nfluids; ++q) if (nm == fluids[q].name) { f = q; break; }
+        if (f == nfluids) throw InvalidArgument("Unable to load pure info for " + names_in[i]);
+        idx[i] = f;
+        m->names.push_back(nm);
+    }
+    auto find_pair = [&](size_t a, size_t b) -> const PR& {
+        for (size_t q = 0; q < npairs; ++q) if (pairs[q].i == a && pairs[q].j == b) return pairs[q];
+        throw InvalidArgument(std::string("Unable to obtain BIP for the pair {") + fluids[a].name + "," + fluids[b].name + "}");
+    };
+    P.nc = (int)N;
+    for (size_t i = 0; i < N; ++i) { P.Tc[i] = fluids[idx[i]].Tc_K; P.vc[i] = 1.0 / fluids[idx[i]].rhoc_molm3; }
+
+    std::vector<RawTerm> raw;
+    // pure-fluid terms (GERG.hpp:117-119)
+    for (size_t i = 0; i < N; ++i) {
+        const F& fl = fluids[idx[i]];
+        for (size_t k = 0; k < fl.n.size(); ++k) {
+            RawTerm r{};
+            r.w = (int)i; r.n = fl.n[k]; r.t = fl.t[k];
+            r.d = (int)fl.d[k]; r.l = (int)fl.l[k]; r.c = fl.c[k];
+            r.kind = (r.c == 0.0) ? GG_POLY : GG_EXP;
+            if (r.kind == GG_POLY) r.l = 0;
+            raw.push_back(r);
+        }
+    }
+    // reducing pairs and departure terms
+    int pidx = 0, ndep = 0;
+    for (size_t i = 0; i < N; ++i) {
+        for (size_t j = i + 1; j < N; ++j, ++pidx) {
+            if (idx[i] == idx[j]) throw InvalidArgument("duplicate component " + names_in[i]);
+            const bool fwd = idx[i] < idx[j];
+            const PR& pr = fwd ? find_pair(idx[i], idx[j]) : find_pair(idx[j], idx[i]);
+            // reversed order: reciprocal betas (GERG.hpp:757-763)
+            const double bT = fwd ? pr.betaT : 1 / pr.betaT, bV = fwd ? pr.betaV : 1 / pr.betaV;
+            const double Tci = P.Tc[i], Tcj = P.Tc[j], vci = P.vc[i], vcj = P.vc[j];
+            const double YT = bT * pr.gammaT * std::sqrt(Tci * Tcj);
+            const double s = std::cbrt(vci) + std::cbrt(vcj);
+            const double YV = 1.0 / 8.0 * bV * pr.gammaV * (s * s * s);
+            P.pair[pidx].beta2T = bT * bT; P.pair[pidx].YT2 = 2.0 * YT;
+            P.pair[pidx].beta2V = bV * bV; P.pair[pidx].YV2 = 2.0 * YV;
+            if (pr.Fij != 0.0) {
+                if (ndep >= kGergMaxDep) throw InvalidArgument("too many departure pairs");
+                P.dep_i[ndep] = (unsigned char)i; P.dep_j[ndep] = (unsigned char)j; P.depF[ndep] = pr.Fij;
+                for (size_t k = 0; k < pr.n.size(); ++k) {
+                    RawTerm r{};
+                    r.w = (int)N + ndep; r.n = pr.n[k]; r.t = pr.t[k]; r.d = (int)pr.d[k];
+                    r.eta = pr.eta[k]; r.eps = pr.epsilon[k]; r.beta = pr.beta[k]; r.gamma = pr.gamma[k];
+                    if (r.eta == 0.0 && r.beta == 0.0) { r.kind = GG_POLY; r.eps = r.gamma = 0; }
+                    else r.kind = GG_GAUSS;
+                    raw.push_back(r);
+                }
+                ++ndep;
+            }
+        }
+    }
+    P.npair = pidx; P.ndep = ndep; P.nw = (int)N + ndep;
+
+    // group by density shape, then by tau exponent
+    using GKey = std::tuple<int, int, int, double, double, double, double, double>;
+    std::map<GKey, std::map<double, std::vector<const RawTerm*>>> groups;
+    for (const auto& r : raw) groups[GKey{r.kind, r.d, r.l, r.c, r.eta, r.eps, r.beta, r.gamma}][r.t].push_back(&r);
+    if (groups.size() > (size_t)kGergMaxGroup) throw InvalidArgument("too many distinct density groups");
+    int g = 0, tq = 0, term = 0;
+    for (const auto& [key, bytau] : groups) {
+        GergGroup& G = P.group[g];
+        G.kind = std::get<0>(key); G.d = std::get<1>(key); G.l = std::get<2>(key);
+        G.c = std::get<3>(key); G.eta = std::get<4>(key); G.eps = std::get<5>(key); G.beta = std::get<6>(key); G.gamma = std::get<7>(key);
+        for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
+        for (const auto& [t, terms] : bytau) {
+            if (tq >= kGergMaxTQ) throw InvalidArgument("too many distinct (group, t) pairs");
+            for (const RawTerm* r : terms) {
+                if (term >= kGergMaxTerm) throw InvalidArgument("too many terms");
+                P.term_n[term] = r->n; P.term_w[term] = (unsigned char)r->w; ++term;
+            }
+            P.tq[tq].t = t; P.tq[tq].term_end = term; ++tq;
+        }
+        G.tq_end = tq;
+        ++g;
+    }
+    P.ngroup = g; P.ntq = tq; P.nterm = term;
+    return m;
+}
+
+}  // namespace
+
+std::unique_ptr<Model> make_gerg_model(const std::string& kind, const Json& spec) {
+    const std::vector<std::string> names = spec.at("names").as_strings();
+    if (kind == "GERG2008resid")
+        return build_gerg("GERG2008resid", names, gerg2008_fluids, sizeof(gerg2008_fluids) / sizeof(gerg2008_fluids[0]), gerg2008_pairs, sizeof(gerg2008_pairs) / sizeof(gerg2008_pairs[0]));
+    if (kind == "GERG2004resid")
+        return build_gerg("GERG2004resid", names, gerg2004_fluids, sizeof(gerg2004_fluids) / sizeof(gerg2004_fluids[0]), gerg2004_pairs, sizeof(gerg2004_pairs) / sizeof(gerg2004_pairs[0]));
+    throw InvalidArgument("unknown GERG kind " + kind);
+}
+
+}  // namespace tq

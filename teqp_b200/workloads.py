@@ -1,0 +1,72 @@
+"""Synthetic state-point workloads of BASELINE.json's configs and the deterministic counter-hash generator,
+in numpy.  The device-side generator (teqpb200_synth_points in csrc/tq_capi.cu) produces the same uniforms from the same
+(seed, point index, stream index), so CPU-side checks and GPU-side benches see the same points.
+
+    u_j(k) = (splitmix64(seed ^ (k * 0x9E3779B97F4A7C15 + j)) >> 11) * 2^-53
+    T = Tlo + (Thi - Tlo) u_0 ;  rho = exp(ln rho_lo + (ln rho_hi - ln rho_lo) u_1)
+    x_i = z0_i exp(0.2 (2 u_{2+i} - 1)) / sum_i(...)
+"""
+import numpy as np
+
+SEED = 20261104
+_M = np.uint64(0xFFFFFFFFFFFFFFFF)
+_G = np.uint64(0x9E3779B97F4A7C15)
+
+
+def _u01(seed, k, j):
+    with np.errstate(over="ignore"):
+        z = np.uint64(seed) ^ (k.astype(np.uint64) * _G + np.uint64(j))
+        z = z + _G
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return (z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def synth_points(npts, k0, Tlo, Thi, rholo, rhohi, z0, seed=SEED):
+    """Returns T[npts], rho[npts], x[ncomp][npts] (float64, C-contiguous)."""
+    k = np.arange(k0, k0 + npts, dtype=np.uint64)
+    T = Tlo + (Thi - Tlo) * _u01(seed, k, 0)
+    rho = np.exp(np.log(rholo) + (np.log(rhohi) - np.log(rholo)) * _u01(seed, k, 1))
+    z0 = np.asarray(z0, dtype=np.float64)
+    x = np.empty((len(z0), npts))
+    s = np.zeros(npts)
+    for i in range(len(z0)):
+        x[i] = z0[i] * np.exp(0.2 * (2.0 * _u01(seed, k, 2 + i) - 1.0))
+        s += x[i]          # summed in index order, then divided (same op order as the device generator)
+    for i in range(len(z0)):
+        x[i] /= s
+    return T, rho, x
+
+
+# AGA8 natural-gas compositions used by the reference's GERG tests (src/tests/catch_test_GERG.cxx:136 and :130), mole percent
+_C3_NAMES = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "isobutane", "n-butane", "isopentane", "n-pentane", "n-hexane"]
+_C3_Z = [96.370276, 0.291926, 0.298014, 1.400282, 0.780001, 0.14425, 0.460146, 0.0759, 0.0549, 0.124306]
+_GERG21 = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "n-butane", "isobutane", "n-pentane", "isopentane", "n-hexane",
+           "n-heptane", "n-octane", "hydrogen", "oxygen", "carbonmonoxide", "water", "helium", "argon", "hydrogensulfide", "n-nonane", "n-decane"]
+
+
+def _norm(z):
+    z = np.asarray(z, dtype=np.float64)
+    return (z / z.sum()).tolist()
+
+
+WORKLOADS = {
+    # C1: Peng-Robinson pure methane (values of src/tests/catch_test_cubics.cxx:28-30), Ar00..Ar04
+    "C1": dict(spec={"kind": "PR", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011]}},
+               T=(100.0, 600.0), rho=(1.0, 25000.0), z0=[1.0], npts=10**6, what="Ar0n", nmax=4, bytes_per_point=56),
+    # C2: PC-SAFT methane + ethane (library values, include/teqp/models/pcsaft.hpp:53-54)
+    "C2": dict(spec={"kind": "PCSAFT", "model": {"names": ["Methane", "Ethane"]}},
+               T=(150.0, 450.0), rho=(1.0, 20000.0), z0=[0.5, 0.5], npts=10**7, what="Arxy+lnphi", bytes_per_point=96),
+    # C3: GERG-2008 10-component natural gas, Ar00..Ar04 -- the headline
+    "C3": dict(spec={"kind": "GERG2008resid", "model": {"names": _C3_NAMES}},
+               T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm(_C3_Z), npts=10**8, what="Ar0n", nmax=4, bytes_per_point=136),
+    # C5 (Ar0n variant): GERG-2008 all 21 components
+    "C5": dict(spec={"kind": "GERG2008resid", "model": {"names": _GERG21}},
+               T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm([1.0] * 21), npts=10**6, what="Ar0n", nmax=4, bytes_per_point=224),
+}
+
+
+def workload_points(name, npts, k0=0):
+    w = WORKLOADS[name]
+    return synth_points(npts, k0, w["T"][0], w["T"][1], w["rho"][0], w["rho"][1], w["z0"])

@@ -1,0 +1,150 @@
+// TEST HARNESS ONLY -- never shipped, never linked into libteqpb200.so, never used by bench.py or the Python package.
+//
+// Replays the per-state-point __host__ __device__ functions of the kernels (gerg_point, cubic_table_point, generic_*_point)
+// in a plain host loop, on the very parameter block the product's JSON ingestion builds.  Purpose: the build container has no
+// GPU, so this lets the CPU-only test tier (-m "not gpu") check the kernels' MATHEMATICS against the oracle before a GPU box is
+// spent on them.  The GPU parity tests (-m gpu) go through the C ABI of libteqpb200.so and do not touch this file.
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../teqp_b200/csrc/tq_common.hpp"
+#include "../../teqp_b200/csrc/tq_cubic.cuh"
+#include "../../teqp_b200/csrc/tq_generic.cuh"
+#include "../../teqp_b200/csrc/tq_gerg.cuh"
+#include "../../teqp_b200/csrc/tq_pcsaft.cuh"
+
+using namespace tq;
+
+namespace {
+void put(const std::string& m, char* e, int n) { if (e && n > 0) { std::strncpy(e, m.c_str(), n - 1); e[n - 1] = 0; } }
+
+template<int NT, int ND>
+void gerg_loop(const GergProgram& P, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
+    std::vector<double> W(P.nw);
+    for (long long k = 0; k < npts; ++k) {
+        for (int i = 0; i < P.nc; ++i) W[i] = x[(long long)i * xs + (xs ? k : 0)];
+        double A[NT + 1][ND + 1];
+        gerg_point<NT, ND>(P, T[k], rho[k], W.data(), 1, A);
+        double fn = 1;
+        for (int n = 0; n <= NT; ++n) {
+            if (n >= 2) fn *= n;
+            double fm = 1;
+            for (int m = 0; m <= ND; ++m) { if (m >= 2) fm *= m; out[(long long)(n * (ND + 1) + m) * npts + k] = fn * fm * A[n][m]; }
+        }
+    }
+}
+
+template<int NT>
+void cubic_loop(const CubicParams& p, int ND, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
+    for (long long k = 0; k < npts; ++k) {
+        double xx[kCubicMaxC];
+        for (int i = 0; i < p.nc; ++i) xx[i] = x[(long long)i * xs + (xs ? k : 0)];
+        cubic_table_point<NT, kCubicMaxC>(p, T[k], rho[k], xx, ND, out + k, npts);
+    }
+}
+
+template<class M, int CT, int CD>
+void generic_loop(const typename M::Params& p, int nc, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
+    for (long long k = 0; k < npts; ++k) {
+        double xx[M::kMaxC];
+        for (int i = 0; i < nc; ++i) xx[i] = x[(long long)i * xs + (xs ? k : 0)];
+        generic_ar_point<M, M::kMaxC, CT, CD>(p, nc, T[k], rho[k], xx, NT, ND, out + k, npts);
+    }
+}
+template<class M>
+void generic_table(const typename M::Params& p, int nc, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
+    if (NT == 0 && ND <= 4) generic_loop<M, 0, 4>(p, nc, NT, ND, npts, T, rho, x, xs, out);
+    else if (NT == 0) generic_loop<M, 0, 6>(p, nc, NT, ND, npts, T, rho, x, xs, out);
+    else if (ND == 0) generic_loop<M, 4, 0>(p, nc, NT, ND, npts, T, rho, x, xs, out);
+    else if (NT <= 2 && ND <= 4) generic_loop<M, 2, 4>(p, nc, NT, ND, npts, T, rho, x, xs, out);
+    else throw InvalidArgument("shape not compiled in the emulation harness");
+}
+template<class M>
+void generic_atrhoxi(const typename M::Params& p, int nc, long long npts, const double* T, const double* rho, const double* x, double* out) {
+    for (long long k = 0; k < npts; ++k) {
+        double xx[M::kMaxC];
+        for (int i = 0; i < nc; ++i) xx[i] = x[(long long)i * npts + k];
+        generic_ATrhoXi_point<M, M::kMaxC>(p, nc, T[k], rho[k], xx, out + k, npts);
+    }
+}
+template<class M>
+void generic_iso(const typename M::Params& p, int nc, long long npts, const double* T, const double* rv, const IsochoricOut& o) {
+    for (long long k = 0; k < npts; ++k) {
+        double r[M::kMaxC];
+        for (int i = 0; i < nc; ++i) r[i] = rv[(long long)i * npts + k];
+        generic_isochoric_point<M, M::kMaxC>(p, nc, T[k], r, o, k, npts);
+    }
+}
+}  // namespace
+
+extern "C" {
+
+// mode 0: Lambda_nm table for the kernel family the product would launch; mode 1: force the generic jet sweep (cubic only)
+int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, const double* T, const double* rho, const double* x,
+                  int ncomp, int broadcast, double* out, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        const long long xs = broadcast ? 0 : npts;
+        if (fam.rfind("GERG", 0) == 0) {
+            const GergProgram& P = *static_cast<const GergProgram*>(blob);
+#define C(a, b) if (NT == a && ND == b) { gerg_loop<a, b>(P, npts, T, rho, x, xs, out); return 0; }
+            C(0, 0) C(0, 1) C(0, 2) C(0, 3) C(0, 4) C(0, 5) C(0, 6) C(1, 0) C(2, 0) C(3, 0) C(4, 0) C(1, 1) C(1, 2) C(2, 1) C(2, 2) C(2, 4)
+#undef C
+            throw InvalidArgument("shape not compiled in the emulation harness");
+        } else if (fam == "cubic" || fam == "vdW") {
+            const CubicParams& p = *static_cast<const CubicParams*>(blob);
+            if (mode == 1) { generic_table<CubicDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out); return 0; }
+            switch (NT) {
+                case 0: cubic_loop<0>(p, ND, npts, T, rho, x, xs, out); break;
+                case 1: cubic_loop<1>(p, ND, npts, T, rho, x, xs, out); break;
+                case 2: cubic_loop<2>(p, ND, npts, T, rho, x, xs, out); break;
+                case 3: cubic_loop<3>(p, ND, npts, T, rho, x, xs, out); break;
+                default: cubic_loop<4>(p, ND, npts, T, rho, x, xs, out); break;
+            }
+            return 0;
+        } else if (fam == "PCSAFT") {
+            const PcsaftParams& p = *static_cast<const PcsaftParams*>(blob);
+            generic_table<PcsaftDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
+        throw InvalidArgument("family not wired in the emulation harness: " + fam);
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const double* rho, const double* x, int ncomp, double* out,
+                       char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else throw InvalidArgument("family not wired in the emulation harness: " + fam);
+        return 0;
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+int emul_isochoric(const char* json, long long npts, const double* T, const double* rhovec, int ncomp, double* f, double* g, double* H,
+                   double* lnphi, double* phi, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        IsochoricOut o; o.Psir = f; o.grad = g; o.hess = H; o.lnphi = lnphi; o.phi = phi;
+        if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else throw InvalidArgument("family not wired in the emulation harness: " + fam);
+        return 0;
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+}  // extern "C"

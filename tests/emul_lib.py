@@ -1,0 +1,64 @@
+"""ctypes front-end of tests/emul/libtq_emul.so (host replay of the kernels' per-point functions; TEST HARNESS ONLY)."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "emul", "libtq_emul.so")
+_dp = C.POINTER(C.c_double)
+_lib = None
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(LIB_PATH)
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(_dp) if a is not None else None
+
+
+def ar_table(spec, NT, ND, T, rho, x, mode=0):
+    T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    n = T.size
+    out = np.empty(((NT + 1) * (ND + 1), n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_ar_table(json.dumps(spec).encode(), C.c_int(mode), C.c_int(NT), C.c_int(ND), C.c_longlong(n), _p(T), _p(rho), _p(x),
+                             C.c_int(x.shape[0]), C.c_int(0), _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out.reshape(NT + 1, ND + 1, n)
+
+
+def ATrhoXi_table(spec, T, rho, x):
+    T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+    x = np.ascontiguousarray(x, dtype=np.float64)
+    n = T.size; nc = x.shape[0]
+    out = np.empty((nc * 36, n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_ATrhoXi_table(json.dumps(spec).encode(), C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(nc), _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out.reshape(nc, 3, 3, 4, n)
+
+
+def isochoric(spec, T, rhovec, hess=True):
+    T = np.ascontiguousarray(T, dtype=np.float64); rv = np.ascontiguousarray(rhovec, dtype=np.float64)
+    n = T.size; nc = rv.shape[0]
+    f = np.empty(n); g = np.empty((nc, n)); H = np.empty((nc * nc, n)) if hess else None
+    lnphi = np.empty((nc, n)); phi = np.empty((nc, n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_isochoric(json.dumps(spec).encode(), C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), _p(f), _p(g), _p(H), _p(lnphi), _p(phi),
+                              err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return f, g, H, lnphi, phi
