@@ -466,3 +466,46 @@ extern "C" int teqpb200_synth_points(const long long int npts, const long long i
         ++g_launches;
     });
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// FP64 FMA-pipe peak of the current device, measured: 8 independent DFMA chains per thread, enough resident warps to saturate the
+// pipe.  This is the denominator of the "% of FP64 peak" figure (MEASURED_PEAKS.json has no FP64 entry).
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double* sink, int iters, double a, double b) {
+    double r0 = threadIdx.x, r1 = r0 + 1, r2 = r0 + 2, r3 = r0 + 3, r4 = r0 + 4, r5 = r0 + 5, r6 = r0 + 6, r7 = r0 + 7;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            r0 = fma(r0, a, b); r1 = fma(r1, a, b); r2 = fma(r2, a, b); r3 = fma(r3, a, b);
+            r4 = fma(r4, a, b); r5 = fma(r5, a, b); r6 = fma(r6, a, b); r7 = fma(r7, a, b);
+        }
+    }
+    const double s = ((r0 + r1) + (r2 + r3)) + ((r4 + r5) + (r6 + r7));
+    if (s == 123.456) sink[0] = s;  // never true; keeps the chains alive
+}
+}  // namespace
+
+extern "C" int teqpb200_fp64_peak(double* tflops, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        double* sink = nullptr;
+        TQ_CUDA(cudaMalloc(&sink, sizeof(double)));
+        const int iters = 4096, block = 256, grid = sm_count() * 8;
+        cudaEvent_t e0, e1;
+        TQ_CUDA(cudaEventCreate(&e0)); TQ_CUDA(cudaEventCreate(&e1));
+        double best = 0.0;
+        for (int rep = 0; rep < 5; ++rep) {
+            TQ_CUDA(cudaEventRecord(e0, 0));
+            dfma_peak_kernel<<<grid, block>>>(sink, iters, 0.999999, 1e-9);
+            TQ_CUDA(cudaEventRecord(e1, 0));
+            TQ_CUDA(cudaEventSynchronize(e1));
+            float ms = 0;
+            TQ_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            const double flops = 2.0 * 64.0 * iters * (double)block * grid;
+            if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+        }
+        TQ_CUDA(cudaEventDestroy(e0)); TQ_CUDA(cudaEventDestroy(e1));
+        TQ_CUDA(cudaFree(sink));
+        *tflops = best;
+    });
+}

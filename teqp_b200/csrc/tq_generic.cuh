@@ -80,16 +80,17 @@ void generic_launch_ar_table_inst(const typename M::Params& p, int nc, int NT, i
     TQ_CUDA(cudaGetLastError());
 }
 
-// picks the smallest compiled jet shape that covers (NT, ND)
+// picks the smallest compiled jet shape that covers (NT, ND).  Split in two so that a heavy model family can instantiate the
+// density-only shapes and the temperature / mixed shapes in separate translation units (parallel compilation).
 template<class M>
-void generic_launch_ar_table(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
-    if (NT < 0 || NT > kMaxDerivT || ND < 0 || ND > kMaxDerivD) throw InvalidArgument("derivative order out of range");
-    if (in.npts == 0) return;
-    if (NT == 0) {
-        if (ND <= 2) generic_launch_ar_table_inst<M, 0, 2>(p, nc, NT, ND, in, out, st);
-        else if (ND <= 4) generic_launch_ar_table_inst<M, 0, 4>(p, nc, NT, ND, in, out, st);
-        else generic_launch_ar_table_inst<M, 0, 6>(p, nc, NT, ND, in, out, st);
-    } else if (ND == 0) {
+void generic_launch_ar_table_rho(const typename M::Params& p, int nc, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
+    if (ND <= 2) generic_launch_ar_table_inst<M, 0, 2>(p, nc, 0, ND, in, out, st);
+    else if (ND <= 4) generic_launch_ar_table_inst<M, 0, 4>(p, nc, 0, ND, in, out, st);
+    else generic_launch_ar_table_inst<M, 0, 6>(p, nc, 0, ND, in, out, st);
+}
+template<class M>
+void generic_launch_ar_table_mixed(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
+    if (ND == 0) {
         if (NT <= 2) generic_launch_ar_table_inst<M, 2, 0>(p, nc, NT, ND, in, out, st);
         else generic_launch_ar_table_inst<M, 4, 0>(p, nc, NT, ND, in, out, st);
     } else if (NT <= 2 && ND <= 2) {
@@ -99,6 +100,16 @@ void generic_launch_ar_table(const typename M::Params& p, int nc, int NT, int ND
     } else {
         throw InvalidArgument("mixed derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is larger than the compiled jet shapes (NT<=2 with ND<=4, or one of them zero)");
     }
+}
+inline void generic_check_ar_shape(int NT, int ND) {
+    if (NT < 0 || NT > kMaxDerivT || ND < 0 || ND > kMaxDerivD) throw InvalidArgument("derivative order out of range");
+}
+template<class M>
+void generic_launch_ar_table(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
+    generic_check_ar_shape(NT, ND);
+    if (in.npts == 0) return;
+    if (NT == 0) generic_launch_ar_table_rho<M>(p, nc, ND, in, out, st);
+    else generic_launch_ar_table_mixed<M>(p, nc, NT, ND, in, out, st);
 }
 
 #endif  // __CUDACC__
@@ -184,10 +195,11 @@ TQ_HD J3<0, B, C> psir_jet(const typename M::Params& p, int nc, double T0, const
             rhotot = rhotot + r[k];
         }
     }
-    const XT inv = trecip(rhotot);
+    // mole fractions by DIVISION, as the reference forms them (derivs.hpp:1039): a reciprocal-multiply differs in the last
+    // bit of x_i, which -ln(1 - b rho) amplifies by 1/(b rho) at low density
 #pragma unroll(MAXN <= 4 ? MAXN : 1)
     for (int k = 0; k < MAXN; ++k)
-        if (k < nc) r[k] = r[k] * inv;  // mole fractions
+        if (k < nc) r[k] = r[k] / rhotot;
     const J3<0, 0, 0> T(T0);
     const XT a = embed<XT>(M::template alphar<MAXN>(p, T, rhotot, r));
     return a * M::R(p, r) * T0 * rhotot;

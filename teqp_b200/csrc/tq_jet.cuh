@@ -204,8 +204,9 @@ template<int N, class T> TQ_HD Tay<N, T> trecip(const Tay<N, T>& b) {
 }
 template<int N, class T> TQ_HD Tay<N, T> operator/(const Tay<N, T>& a, const Tay<N, T>& b) {
     Tay<N, T> r;
+    r.c[0] = a.c[0] / b.c[0];  // true division for the base value (bit-faithful to the reference's a/b); reciprocal for the rest
+    if (N == 0) return r;
     const T inv = trecip(b.c[0]);
-    r.c[0] = a.c[0] * inv;
 #pragma unroll
     for (int k = 1; k <= N; ++k) {
         T s = a.c[k];

@@ -8,6 +8,12 @@
 
 namespace tq {
 
+// the kernels live in tq_pcsaft_k{1..4}.cu (one translation unit per jet-shape group, compiled in parallel)
+void pcsaft_launch_ar_rho(const PcsaftParams&, int ND, const DeviceBatch&, double*, cudaStream_t);
+void pcsaft_launch_ar_mixed(const PcsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
+void pcsaft_launch_ATrhoXi(const PcsaftParams&, const DeviceBatch&, double*, cudaStream_t);
+void pcsaft_launch_isochoric(const PcsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+
 namespace {
 
 // universal model constants, published tables (see header comment of tq_pcsaft.cuh)
@@ -48,14 +54,13 @@ public:
     double R(const double*, int) const override { return p.R; }
     const void* params_blob(size_t* n) const override { *n = sizeof(p); return &p; }
     void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override {
-        generic_launch_ar_table<PcsaftDev>(p, p.nc, NT, ND, in, out, st);
+        generic_check_ar_shape(NT, ND);
+        if (in.npts == 0) return;
+        if (NT == 0) pcsaft_launch_ar_rho(p, ND, in, out, st);
+        else pcsaft_launch_ar_mixed(p, NT, ND, in, out, st);
     }
-    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override {
-        generic_launch_ATrhoXi<PcsaftDev>(p, p.nc, in, out, st);
-    }
-    void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
-        generic_launch_isochoric<PcsaftDev>(p, p.nc, in, o, st);
-    }
+    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { pcsaft_launch_ATrhoXi(p, in, out, st); }
+    void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { pcsaft_launch_isochoric(p, in, o, st); }
 };
 
 }  // namespace

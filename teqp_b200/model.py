@@ -1,0 +1,212 @@
+"""AbstractModel mirror over the C ABI.  Method names follow teqp::cppinterface::AbstractModel
+(/root/reference/include/teqp/cpp/teqpcpp.hpp:94-191): get_Ar00..get_Ar24, get_Ar0{1..6}n, get_Ar{1..4}0n, get_Arxy,
+get_ATrhoXi, get_R, get_fugacity_coefficients, build_Psir_gradient_autodiff, build_Psir_Hessian_autodiff,
+build_Psir_fgradHessian_autodiff -- scalar calls are batches of one state point on the GPU.  The *_batch methods are the new
+array entry points."""
+import ctypes as C
+import json
+
+import numpy as np
+
+from . import BROADCAST_X, DEVICE_PTRS, TeqpError, _Arg, _check, _dp, _ip, _is_torch, lib
+
+
+def _torch_stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class Model:
+    def __init__(self, spec):
+        self.spec = spec if isinstance(spec, str) else json.dumps(spec)
+        self._uuid = C.c_longlong(-1)
+        err = C.create_string_buffer(2000)
+        _check(lib().build_model(self.spec.encode(), C.byref(self._uuid), err, C.c_int(2000)), err)
+        n = C.c_int(0)
+        _check(lib().teqpb200_get_ncomp(self._uuid, C.byref(n), err, C.c_int(2000)), err)
+        self.ncomp = n.value
+
+    def __del__(self):
+        try:
+            if self._uuid.value >= 0:
+                err = C.create_string_buffer(200)
+                lib().free_model(self._uuid, err, C.c_int(200))
+                self._uuid = C.c_longlong(-1)
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _prep(self, T, rho, x):
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        xs = tuple(x.shape)
+        if len(xs) == 1:
+            flags |= BROADCAST_X
+            nc = xs[0]
+        else:
+            nc = xs[0]
+            assert xs[1] == n, "molefrac must be [Ncomp][npts] (or [Ncomp] to broadcast)"
+        return dev, flags, n, nc, _Arg(T, dev), _Arg(rho, dev), _Arg(x, dev)
+
+    def _out(self, shape, dev, like, out=None):
+        if out is not None:
+            return out
+        if dev:
+            import torch
+            return torch.empty(shape, dtype=torch.float64, device=like.device)
+        return np.empty(shape)
+
+    def _enter(self, dev):
+        if dev:
+            lib().teqpb200_set_stream(_torch_stream_ptr())
+
+    # ------------------------------------------------------------------ batched entry points
+    def get_Ar0n_batch(self, nmax, T, rho, x, out=None):
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((nmax + 1, n), dev, T, out)
+        ao = _Arg(out, dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_Ar0n_batch(self._uuid, C.c_int(nmax), C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), ao.ptr,
+                                    C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_Arn0_batch(self, nmax, T, rho, x, out=None):
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((nmax + 1, n), dev, T, out)
+        ao = _Arg(out, dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_Arn0_batch(self._uuid, C.c_int(nmax), C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), ao.ptr,
+                                    C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_Arxy_batch(self, pairs, T, rho, x, out=None):
+        """pairs: list of (NT, ND); returns [len(pairs)][npts]"""
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((len(pairs), n), dev, T, out)
+        ao = _Arg(out, dev)
+        NT = (C.c_int * len(pairs))(*[p[0] for p in pairs])
+        ND = (C.c_int * len(pairs))(*[p[1] for p in pairs])
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_Arxy_batch(self._uuid, C.c_int(len(pairs)), NT, ND, C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), ao.ptr,
+                                    C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_ATrhoXi_table_batch(self, T, rho, x, out=None):
+        """returns [Ncomp][3][3][4][npts]: index (i, NT, ND, NXi)"""
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((nc, 3, 3, 4, n), dev, T, out)
+        ao = _Arg(out, dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_ATrhoXi_table_batch(self._uuid, C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), ao.ptr, C.c_int(flags),
+                                             err, C.c_int(2000)), err)
+        return ao.obj
+
+    def _iso(self, fn, T, rhovec, nrows_list):
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        nc = rhovec.shape[0]
+        aT, av = _Arg(T, dev), _Arg(rhovec, dev)
+        outs = [_Arg(self._out((r, n) if r > 1 or True else (n,), dev, T), dev) for r in nrows_list]
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(fn(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *[o.ptr for o in outs], C.c_int(flags), err, C.c_int(2000)), err)
+        return [o.obj for o in outs]
+
+    def build_Psir_fgradHessian_batch(self, T, rhovec):
+        nc = rhovec.shape[0]
+        f, g, H = self._iso(lib().build_Psir_fgradHessian_batch, T, rhovec, [1, nc, nc * nc])
+        return f[0], g, H.reshape((nc, nc) + tuple(H.shape[1:]))
+
+    def get_ln_fugacity_coefficients_batch(self, T, rhovec):
+        return self._iso(lib().get_ln_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]])[0]
+
+    def get_fugacity_coefficients_batch(self, T, rhovec):
+        return self._iso(lib().get_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]])[0]
+
+    # ------------------------------------------------------------------ reference scalar surface
+    def get_R(self, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().teqpb200_get_R(self._uuid, z.ctypes.data_as(_dp), C.c_int(z.size), C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_Arxy(self, NT, ND, T, rho, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().get_Arxy(self._uuid, C.c_int(NT), C.c_int(ND), C.c_double(T), C.c_double(rho), z.ctypes.data_as(_dp), C.c_int(z.size),
+                              C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_ATrhoXi(self, T, NT, rho, ND, molefrac, i, NXi):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().get_ATrhoXi(self._uuid, C.c_double(T), C.c_int(NT), C.c_double(rho), C.c_int(ND), z.ctypes.data_as(_dp), C.c_int(z.size),
+                                 C.c_int(i), C.c_int(NXi), C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def _one(self, T, rho, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64).reshape(-1, 1)
+        return np.array([float(T)]), np.array([float(rho)]), z
+
+    def get_fugacity_coefficients(self, T, rhovec):
+        rv = np.ascontiguousarray(rhovec, dtype=np.float64).reshape(-1, 1)
+        return self.get_fugacity_coefficients_batch(np.array([float(T)]), rv)[:, 0]
+
+    def build_Psir_gradient_autodiff(self, T, rhovec):
+        rv = np.ascontiguousarray(rhovec, dtype=np.float64).reshape(-1, 1)
+        return self.build_Psir_fgradHessian_batch(np.array([float(T)]), rv)[1][:, 0]
+
+    def build_Psir_Hessian_autodiff(self, T, rhovec):
+        rv = np.ascontiguousarray(rhovec, dtype=np.float64).reshape(-1, 1)
+        return self.build_Psir_fgradHessian_batch(np.array([float(T)]), rv)[2][:, :, 0]
+
+    def build_Psir_fgradHessian_autodiff(self, T, rhovec):
+        rv = np.ascontiguousarray(rhovec, dtype=np.float64).reshape(-1, 1)
+        f, g, H = self.build_Psir_fgradHessian_batch(np.array([float(T)]), rv)
+        return float(f[0]), g[:, 0], H[:, :, 0]
+
+
+def _add_scalar_methods():
+    # get_Ar{i}{j}(T, rho, z) -> double (teqpcpp.hpp:22-37,107-109); get_Ar0{n}n / get_Ar{n}0n -> array (:39-51,111-117)
+    def mk_ij(i, j):
+        def f(self, T, rho, molefrac):
+            Tn, rn, z = self._one(T, rho, molefrac)
+            return float(self.get_Arxy_batch([(i, j)], Tn, rn, z)[0, 0])
+        f.__name__ = "get_Ar%d%d" % (i, j)
+        return f
+    for i in range(3):
+        for j in range(5):
+            setattr(Model, "get_Ar%d%d" % (i, j), mk_ij(i, j))
+
+    def mk_0n(n):
+        def f(self, T, rho, molefrac):
+            Tn, rn, z = self._one(T, rho, molefrac)
+            return self.get_Ar0n_batch(n, Tn, rn, z)[:, 0].copy()
+        return f
+
+    def mk_n0(n):
+        def f(self, T, rho, molefrac):
+            Tn, rn, z = self._one(T, rho, molefrac)
+            return self.get_Arn0_batch(n, Tn, rn, z)[:, 0].copy()
+        return f
+    for n in range(1, 7):
+        setattr(Model, "get_Ar0%dn" % n, mk_0n(n))
+    for n in range(1, 5):
+        setattr(Model, "get_Ar%d0n" % n, mk_n0(n))
+
+
+_add_scalar_methods()
+
+
+def make_model(spec, validate=True):
+    """teqp.make_model(json) equivalent (/root/reference/teqp/__init__.py:42-49); `validate` is accepted for signature parity."""
+    return Model(spec)

@@ -70,3 +70,12 @@ WORKLOADS = {
 def workload_points(name, npts, k0=0):
     w = WORKLOADS[name]
     return synth_points(npts, k0, w["T"][0], w["T"][1], w["rho"][0], w["rho"][1], w["z0"])
+
+
+def shard_range(npts, rank, world):
+    """Contiguous even split of [0, npts) over `world` ranks / devices, remainder to the last one -- the same rule the
+    multi-device host driver in csrc/tq_capi.cu (run_host) applies."""
+    per = npts // world
+    a = per * rank
+    b = npts if rank == world - 1 else a + per
+    return a, b

@@ -1,0 +1,59 @@
+"""The parity rule used by every test (DESIGN.md "Parity rule"):
+
+    |got - ref| <= RTOL * |ref| + RTOL * S ,   RTOL = 1e-12
+
+S is the absolute floor "near zero-valued derivatives" that BASELINE.json's north_star allows: the scale of the derivative
+family at that state point.  It is needed because (a) a derivative that crosses zero has no meaningful relative error, and
+(b) the reference's own Taylor arithmetic carries rounding noise of eps * (family scale) in its high-order coefficients
+(e.g. Ar04 of a term ~ delta^1 is exactly 0 analytically but eps-sized in exp(d ln delta) arithmetic), so two correct
+implementations differ by that much.  Both the reference and the kernels work in TAYLOR-COEFFICIENT space
+(c_nm = Lambda_nm / (n! m!)), so the family scale is taken there: S_nm = n! m! max_ij |Lambda_ij| / (i! j!).
+The helper reports how often the floor was needed so a test can bound it."""
+import numpy as np
+
+RTOL = 1e-12
+
+
+def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=1.0):
+    got = np.asarray(got, dtype=np.float64); ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape, (name, got.shape, ref.shape)
+    fin_r, fin_g = np.isfinite(ref), np.isfinite(got)
+    assert np.array_equal(fin_r, fin_g), "%s: finite/non-finite pattern differs at %d points" % (name, int(np.sum(fin_r != fin_g)))
+    if scale is None:
+        scale = 0.0
+    scale = np.broadcast_to(np.asarray(scale, dtype=np.float64), ref.shape)
+    d = np.where(fin_r, np.abs(got - ref), 0.0)
+    a = np.where(fin_r, np.abs(ref), 1.0)
+    s = np.where(np.isfinite(scale), scale, 0.0)
+    tol = rtol * a + rtol * s
+    bad = d > tol
+    if np.any(bad):
+        i = np.unravel_index(np.argmax(d / np.maximum(tol, 1e-300)), d.shape)
+        raise AssertionError("%s: %d of %d outside tolerance; worst at %s: got %.17g ref %.17g |d| %.3e tol %.3e"
+                             % (name, int(bad.sum()), d.size, i, got[i], ref[i], d[i], tol[i]))
+    floor_frac = float(np.mean(d > rtol * a))
+    assert floor_frac <= max_floor_frac, "%s: %.3f of the points needed the absolute floor (limit %.3f)" % (name, floor_frac, max_floor_frac)
+    return floor_frac
+
+
+def family_scale(table, axes):
+    """max |entry| over the given axes of a derivative table (the per-point family scale)."""
+    t = np.where(np.isfinite(table), np.abs(table), 0.0)
+    return np.max(t, axis=axes)
+
+
+_FACT = [1.0, 1.0, 2.0, 6.0, 24.0, 120.0, 720.0]
+
+
+def coeff_scale(table):
+    """table[n][m][npts] of Lambda_nm -> per-point max |Lambda_nm| / (n! m!)  (family scale in Taylor-coefficient space)"""
+    t = np.where(np.isfinite(table), np.abs(table), 0.0)
+    s = np.zeros(t.shape[-1])
+    for n in range(t.shape[0]):
+        for m in range(t.shape[1]):
+            s = np.maximum(s, t[n, m] / (_FACT[n] * _FACT[m]))
+    return s
+
+
+def fact(n, m=0):
+    return _FACT[n] * _FACT[m]

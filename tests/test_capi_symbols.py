@@ -1,0 +1,81 @@
+"""CPU tier: the C-ABI library loads and exports every function include/teqpb200.h declares; model construction, handle and
+error-code behaviour of the reference interface (teqpc.cpp:45-103) -- no kernel is launched here."""
+import ctypes as C
+import json
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    src = open(os.path.join(ROOT, "include", "teqpb200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(?:int|void\*?|long long int)\s+\*?\s*([A-Za-z_][A-Za-z0-9_]*)\s*\(", src)))
+
+
+def test_every_declared_symbol_is_exported():
+    import teqp_b200
+    lib = teqp_b200.lib()
+    names = declared_functions()
+    assert "build_model" in names and "get_Ar0n_batch" in names and len(names) >= 25
+    for n in names:
+        assert hasattr(lib, n), "libteqpb200.so does not export " + n
+
+
+def test_build_free_and_error_codes():
+    import teqp_b200
+    lib = teqp_b200.lib()
+    err = C.create_string_buffer(200)
+    uid = C.c_longlong(-1)
+    ok = {"kind": "GERG2008resid", "model": {"names": ["methane", "ethane", "nitrogen"]}}
+    assert lib.build_model(json.dumps(ok).encode(), C.byref(uid), err, 200) == 0 and uid.value >= 0
+    first = uid.value
+    assert lib.build_model(json.dumps(ok).encode(), C.byref(uid), err, 200) == 0 and uid.value == first + 1   # atomic counter
+    n = C.c_int()
+    assert lib.teqpb200_get_ncomp(C.c_longlong(first), C.byref(n), err, 200) == 0 and n.value == 3
+    # unknown kind / bad names -> code 30 "Unable to load with error:" (teqpc.cpp:83-85)
+    assert lib.build_model(b'{"kind": "nope", "model": {}}', C.byref(uid), err, 200) == 30
+    assert err.value.startswith(b"Unable to load with error:")
+    assert lib.build_model(json.dumps({"kind": "GERG2008resid", "model": {"names": ["unobtainium"]}}).encode(), C.byref(uid), err, 200) == 30
+    # malformed JSON -> 9999 (any std::exception)
+    assert lib.build_model(b'{"kind": ', C.byref(uid), err, 200) == 9999
+    # message longer than the buffer (teqpc.cpp:50-60)
+    small = C.create_string_buffer(40)
+    assert lib.build_model(b'{"kind": "nope", "model": {}}', C.byref(uid), small, 40) == 30
+    assert small.value == b"Error message too long for buffer"
+    tiny = C.create_string_buffer(5)
+    assert lib.build_model(b'{"kind": "nope", "model": {}}', C.byref(uid), tiny, 5) == 30 and tiny.value == b"?"
+    # freeing: unknown ids are not an error (teqpc.cpp:94-103)
+    assert lib.free_model(C.c_longlong(first), err, 200) == 0
+    assert lib.free_model(C.c_longlong(123456789), err, 200) == 0
+    assert lib.teqpb200_get_ncomp(C.c_longlong(first), C.byref(n), err, 200) == 9999
+
+
+@pytest.mark.parametrize("spec", [
+    {"kind": "vdW1", "model": {"a": 0.2283, "b": 4.278e-5}},
+    {"kind": "vdW", "model": {"Tcrit / K": [190.564, 305.322], "pcrit / Pa": [4599200, 4872200]}},
+    {"kind": "PR", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011]}},
+    {"kind": "SRK", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011], "kmat": [[0.0]]}},
+    {"kind": "cubic", "model": {"type": "PR", "Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011], "alpha": [{"type": "PR78", "acentric": 0.011}]}},
+    {"kind": "PCSAFT", "model": {"names": ["Methane", "Ethane"], "kmat": [[0, 0.01], [0.01, 0]]}},
+    {"kind": "GERG2004resid", "model": {"names": ["methane", "Nitrogen"]}},
+])
+def test_model_kinds_build(spec):
+    import teqp_b200
+    m = teqp_b200.make_model(spec)
+    assert m.ncomp >= 1 and m.get_R([1.0 / m.ncomp] * m.ncomp) > 8.3
+
+
+def test_bad_model_specs_raise():
+    import teqp_b200
+    for spec in [{"kind": "PR", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200, 1], "acentric": [0.011]}},
+                 {"kind": "cubic", "model": {"type": "XYZ", "Tcrit / K": [1], "pcrit / Pa": [1], "acentric": [0]}},
+                 {"kind": "PCSAFT", "model": {"names": ["Kryptonite"]}},
+                 {"kind": "PCSAFT", "model": {"names": ["Methane"], "ab": "nobody"}},
+                 {"kind": "PR", "model": {"Tcrit / K": [190.564, 305.322], "pcrit / Pa": [4599200, 4872200], "acentric": [0.011, 0.099], "kmat": [[0, 1]]}}]:
+        with pytest.raises(teqp_b200.TeqpError) as e:
+            teqp_b200.make_model(spec)
+        assert e.value.code == 30

@@ -1,0 +1,123 @@
+"""GPU tier (-m gpu): the CUDA kernels through the C ABI of libteqpb200.so against the oracle and the golden files, plus
+size-independent properties at large batch sizes and the reference's scalar C interface."""
+import ctypes as C
+import json
+
+import numpy as np
+import pytest
+
+import cases
+import parity
+import parity_suite as ps
+
+pytestmark = pytest.mark.gpu
+
+AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2"]
+
+
+@pytest.fixture(scope="module")
+def be():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return ps.GpuBackend()
+
+
+@pytest.mark.parametrize("name", AR_CASES)
+def test_ar_tables(be, oracle, name):
+    ps.ar_tables(be, oracle, name, n=3000)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k"])
+def test_atrhoxi(be, oracle, name):
+    ps.atrhoxi(be, oracle, name, n=400)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k"])
+def test_isochoric(be, oracle, name):
+    ps.isochoric(be, oracle, name, n=600)
+
+
+def test_gerg_vs_aga8_golden(be):
+    ps.gerg_vs_aga8_golden(be)
+
+
+def test_edge_cases(be, oracle):
+    ps.edge_cases(be, oracle)
+
+
+def test_headline_parity_100k(be, oracle):
+    """the bench workload itself (C3), 10^5 points of the same synthetic stream, all five outputs"""
+    spec, T, rho, x = cases.points("GERG10", 100000)
+    ref = oracle.RefModel(spec).Ar0n(4, T, rho, x)
+    got = be.model(spec).get_Ar0n_batch(4, T, rho, x)
+    fam = parity.coeff_scale(ref[None])
+    for k in range(5):
+        parity.check("C3 Ar0%d" % k, got[k], ref[k], fam * parity.fact(k), max_floor_frac=(0.02 if k < 3 else 1.0))
+
+
+def test_device_pointers_match_host_pointers_and_shards(be):
+    """device-resident call == host-buffer call bit for bit; a batch evaluated in two shards == the whole batch (what the
+    multi-GPU split relies on); broadcast composition == replicated composition"""
+    import torch
+    spec, T, rho, x = cases.points("GERG10", 200001)
+    m = be.model(spec)
+    host = m.get_Ar0n_batch(4, T, rho, x)
+    dT, dr, dx = (torch.from_numpy(a).cuda() for a in (T, rho, x))
+    dev = m.get_Ar0n_batch(4, dT, dr, dx)
+    torch.cuda.synchronize()
+    assert np.array_equal(dev.cpu().numpy(), host)
+    h = 77777
+    a = m.get_Ar0n_batch(4, T[:h].copy(), rho[:h].copy(), np.ascontiguousarray(x[:, :h]))
+    b = m.get_Ar0n_batch(4, T[h:].copy(), rho[h:].copy(), np.ascontiguousarray(x[:, h:]))
+    assert np.array_equal(np.concatenate([a, b], axis=1), host)
+    z = np.ascontiguousarray(x[:, 0])
+    xb = np.tile(z[:, None], (1, T.size))
+    assert np.array_equal(m.get_Ar0n_batch(4, T, rho, z), m.get_Ar0n_batch(4, T, rho, xb))
+
+
+def test_large_batch_properties(be):
+    """2*10^7 points resident on the device: finite everywhere, and scale invariance of the synthetic stream order
+    (evaluating a permuted batch permutes the result) -- properties that do not need the oracle at full size"""
+    import torch
+    spec = cases.SPECS["GERG10"][0]
+    m = be.model(spec)
+    n = 20_000_000
+    g = torch.Generator(device="cuda").manual_seed(1)
+    T = 250 + 200 * torch.rand(n, dtype=torch.float64, device="cuda", generator=g)
+    rho = torch.exp(np.log(10.0) + (np.log(25000.0) - np.log(10.0)) * torch.rand(n, dtype=torch.float64, device="cuda", generator=g))
+    z = torch.tensor(cases.SPECS["GERG10"][3], dtype=torch.float64, device="cuda")
+    out = m.get_Ar0n_batch(4, T, rho, z)
+    assert bool(torch.isfinite(out).all())
+    perm = torch.randperm(n, device="cuda", generator=g)
+    out2 = m.get_Ar0n_batch(4, T[perm].contiguous(), rho[perm].contiguous(), z)
+    assert bool((out[:, perm] == out2).all())
+
+
+def test_reference_c_abi_scalar_calls(be, oracle):
+    """the reference's own C interface (teqpc.h): build_model / get_Arxy / get_ATrhoXi / free_model, as test_teqpc.py drives it"""
+    import teqp_b200
+    lib = teqp_b200.lib()
+    spec = {"kind": "PR", "model": {"Tcrit / K": [190.564, 305.322], "pcrit / Pa": [4599200, 4872200], "acentric": [0.011, 0.099]}}
+    uid = C.c_longlong(-1); err = C.create_string_buffer(300)
+    assert lib.build_model(json.dumps(spec).encode(), C.byref(uid), err, 300) == 0
+    z = (C.c_double * 2)(0.4, 0.6)
+    val = C.c_double()
+    ref = oracle.RefModel(spec)
+    for NT, ND in [(0, 0), (0, 1), (0, 2), (0, 3), (1, 0), (1, 1), (1, 2), (2, 0), (2, 1), (3, 0)]:
+        assert lib.get_Arxy(uid, NT, ND, C.c_double(300.0), C.c_double(3000.0), z, 2, C.byref(val), err, 300) == 0, err.value
+        r = ref.Arxy(NT, ND, np.array([300.0]), np.array([3000.0]), np.array([[0.4], [0.6]]))[0]
+        assert val.value == pytest.approx(r, rel=1e-12, abs=1e-15)
+    assert lib.get_Arxy(uid, 2, 2, C.c_double(300.0), C.c_double(3000.0), z, 2, C.byref(val), err, 300) == 9999   # unsupported combo
+    assert lib.get_ATrhoXi(uid, C.c_double(300.0), 1, C.c_double(3000.0), 1, z, 2, 1, 2, C.byref(val), err, 300) == 0
+    r = ref.ATrhoXi(1, 1, 1, 2, np.array([300.0]), np.array([3000.0]), np.array([[0.4], [0.6]]))[0]
+    assert val.value == pytest.approx(r, rel=1e-11)
+    assert lib.get_Arxy(uid, 0, 1, C.c_double(300.0), C.c_double(3000.0), z, 3, C.byref(val), err, 300) == 9999     # wrong Ncomp
+    assert lib.free_model(uid, err, 300) == 0
+    assert lib.get_Arxy(uid, 0, 1, C.c_double(300.0), C.c_double(3000.0), z, 2, C.byref(val), err, 300) == 9999     # freed handle
+    # python-side mirror of AbstractModel
+    m = teqp_b200.make_model(spec)
+    v = m.get_Ar04n(300.0, 3000.0, [0.4, 0.6])
+    r = ref.Ar0n(4, np.array([300.0]), np.array([3000.0]), np.array([[0.4], [0.6]]))[:, 0]
+    np.testing.assert_allclose(v, r, rtol=1e-12)
+    assert m.get_Ar11(300.0, 3000.0, [0.4, 0.6]) == pytest.approx(ref.ArNM(1, 1, np.array([300.0]), np.array([3000.0]), np.array([[0.4], [0.6]]))[0], rel=1e-12)
+    assert m.get_R([0.4, 0.6]) == 8.31446261815324
