@@ -200,7 +200,7 @@ void run(int flags, long long npts, const std::vector<HostIn>& ins, const std::v
 
 DeviceBatch make_batch(long long n, const double* T, const double* rho, const double* x, bool broadcast) {
     DeviceBatch b;
-    b.npts = n; b.T = T; b.rho = rho; b.x = x; b.x_stride = broadcast ? 0 : n;
+    b.npts = n; b.T = T; b.rho = rho; b.x = x; b.x_stride = broadcast ? 1 : n; b.x_bcast = broadcast ? 1 : 0;
     return b;
 }
 

@@ -38,13 +38,14 @@ constexpr int kMaxDerivT = 4;   // highest order in 1/T any entry point asks for
 constexpr int kMaxDerivD = 6;   // highest order in rho (get_Ar06n)
 
 // A batch of state points resident on ONE device, structure-of-arrays:
-//   T[npts], rho[npts], x[ncomp][npts]  (x_stride = npts) -- or x[ncomp] broadcast to all points (x_stride = 0).
+//   T[npts], rho[npts], x[ncomp][npts]  (x_stride = npts) -- or x[ncomp] broadcast to all points (x_stride = 1, x_bcast = 1).
 struct DeviceBatch {
     long long npts = 0;
     const double* T = nullptr;
     const double* rho = nullptr;
     const double* x = nullptr;
-    long long x_stride = 0;  // distance between component rows; 0 = one composition for every point
+    long long x_stride = 0;  // distance between component rows
+    int x_bcast = 0;         // 1: one composition x[ncomp] for every point (x_stride = 1)
 };
 
 // What an isochoric-family launch should write; null pointers are skipped.  rhovec is x*rho formed in-kernel exactly as

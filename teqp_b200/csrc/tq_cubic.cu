@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) cubic_ar_table_kernel(const __grid_consta
         double x[MAXN];
 #pragma unroll(MAXN <= 4 ? MAXN : 1)
         for (int i = 0; i < MAXN; ++i)
-            if (i < p.nc) x[i] = __ldg(in.x + (long long)i * in.x_stride + (in.x_stride ? k : 0));
+            if (i < p.nc) x[i] = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
         cubic_table_point<NT, MAXN>(p, T, rho, x, ND, out + k, npts);
     }
 }

@@ -53,7 +53,7 @@ template<class M, int MAXN>
 __device__ __forceinline__ void load_x(double (&x)[MAXN], const int nc, const DeviceBatch& in, const long long k) {
 #pragma unroll(MAXN <= 4 ? MAXN : 1)
     for (int i = 0; i < MAXN; ++i)
-        if (i < nc) x[i] = __ldg(in.x + (long long)i * in.x_stride + (in.x_stride ? k : 0));
+        if (i < nc) x[i] = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
 }
 
 template<class M, int MAXN, int CT, int CD>

@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_cons
     for (long long k = (long long)blockIdx.x * kBlock + threadIdx.x; k < npts; k += stride) {
         const double T = __ldg(in.T + k);
         const double rho = __ldg(in.rho + k);
-        for (int i = 0; i < P.nc; ++i) W[i * kBlock] = __ldg(in.x + (long long)i * in.x_stride + (in.x_stride ? k : 0));
+        for (int i = 0; i < P.nc; ++i) W[i * kBlock] = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
         double A[NT + 1][ND + 1];
         gerg_point<NT, ND>(P, T, rho, W, kBlock, A);
         double fn = 1.0;
