@@ -28,7 +28,7 @@ struct GergPair {
 };
 #include "data/gerg_tables.inc"
 
-constexpr int kBlock = 128;
+constexpr int kBlock = kGergWS;
 
 // ---------------------------------------------------------------------------------------------------------------------
 // device
@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_cons
                                                                double* __restrict__ out) {
     extern __shared__ double Wsh[];  // [nw][kBlock]; each thread touches only its own column -> no barriers needed
     double* W = Wsh + threadIdx.x;
+    const ExpK K = ExpK::load(in.npts >> 62);  // npts < 2^62: the shift is 0, but only at run time
     const long long npts = in.npts;
     const long long stride = (long long)gridDim.x * kBlock;
     for (long long k = (long long)blockIdx.x * kBlock + threadIdx.x; k < npts; k += stride) {
@@ -45,7 +46,7 @@ __global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_cons
         const double rho = __ldg(in.rho + k);
         for (int i = 0; i < P.nc; ++i) W[i * kBlock] = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
         double A[NT + 1][ND + 1];
-        gerg_point<NT, ND>(P, T, rho, W, kBlock, A);
+        gerg_point<NT, ND>(P, K, T, rho, W, A);
         double fn = 1.0;
 #pragma unroll
         for (int n = 0; n <= NT; ++n) {
@@ -181,28 +182,32 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
     P.npair = pidx; P.ndep = ndep; P.nw = (int)N + ndep;
 
     // group by density shape, then by tau exponent
-    using GKey = std::tuple<int, int, int, double, double, double, double, double>;
+    // key = (exponent shape h, then d): groups that share h are consecutive, d ascending (running product of delta)
+    using GKey = std::tuple<int, int, double, double, double, double, double, int>;
     std::map<GKey, std::map<double, std::vector<const RawTerm*>>> groups;
-    for (const auto& r : raw) groups[GKey{r.kind, r.d, r.l, r.c, r.eta, r.eps, r.beta, r.gamma}][r.t].push_back(&r);
+    for (const auto& r : raw) groups[GKey{r.kind, r.l, r.c, r.eta, r.eps, r.beta, r.gamma, r.d}][r.t].push_back(&r);
     if (groups.size() > (size_t)kGergMaxGroup) throw InvalidArgument("too many distinct density groups");
-    int g = 0, tq = 0, term = 0;
+    int g = 0, tq = 0, term = 0, rec = 0;
     for (const auto& [key, bytau] : groups) {
         GergGroup& G = P.group[g];
-        G.kind = std::get<0>(key); G.d = std::get<1>(key); G.l = std::get<2>(key);
-        G.c = std::get<3>(key); G.eta = std::get<4>(key); G.eps = std::get<5>(key); G.beta = std::get<6>(key); G.gamma = std::get<7>(key);
-        for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
-        for (const auto& [t, terms] : bytau) {
-            if (tq >= kGergMaxTQ) throw InvalidArgument("too many distinct (group, t) pairs");
-            for (const RawTerm* r : terms) {
-                if (term >= kGergMaxTerm) throw InvalidArgument("too many terms");
-                P.term_n[term] = r->n; P.term_w[term] = (unsigned char)r->w; ++term;
-            }
-            P.tq[tq].t = t; P.tq[tq].term_end = term; ++tq;
+        G.kind = std::get<0>(key); G.l = std::get<1>(key); G.d = std::get<7>(key);
+        G.c = std::get<2>(key); G.eta = std::get<3>(key); G.eps = std::get<4>(key); G.beta = std::get<5>(key); G.gamma = std::get<6>(key);
+        G.new_h = 1;
+        if (g > 0) {
+            const GergGroup& Q = P.group[g - 1];
+            if (Q.kind == G.kind && Q.l == G.l && Q.c == G.c && Q.eta == G.eta && Q.eps == G.eps && Q.beta == G.beta && Q.gamma == G.gamma && Q.d <= G.d) G.new_h = 0;
         }
-        G.tq_end = tq;
+        for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
+        G.ntq = (int)bytau.size();
+        for (const auto& [t, terms] : bytau) {
+            if (rec + 1 + (int)terms.size() > kGergMaxRec) throw InvalidArgument("too many terms for the device term program");
+            P.rec[rec].val = t; P.rec[rec].a = (int)terms.size(); ++rec;
+            for (const RawTerm* r : terms) { P.rec[rec].val = r->n; P.rec[rec].a = r->w * kGergWS; ++rec; ++term; }
+            ++tq;
+        }
         ++g;
     }
-    P.ngroup = g; P.ntq = tq; P.nterm = term;
+    P.ngroup = g; P.ntq = tq; P.nterm = term; P.nrec = rec;
     return m;
 }
 

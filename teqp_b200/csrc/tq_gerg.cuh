@@ -14,8 +14,12 @@
 // with W = (x_1..x_N, x_i x_j F_ij ...).  Only G_g needs Taylor arithmetic in delta (one exp per group), tau^t needs one exp
 // per distinct (g,t), and each individual term costs ONE fused multiply-add.  Temperature derivatives are free:
 // tau^n d^n(tau^t)/dtau^n = t(t-1)..(t-n+1) tau^t.
+//
+// Groups are sorted by exponent shape and then by d, so that the Taylor coefficients of exp(h(delta)) are computed once per
+// distinct shape (new_h flag) and delta^d is a running product.  Exponentials use tq::fast_exp (tq_math.cuh).
 #pragma once
 #include "tq_jet.cuh"
+#include "tq_math.cuh"
 
 namespace tq {
 
@@ -23,10 +27,10 @@ constexpr int kGergMaxC = 21;
 constexpr int kGergMaxPair = kGergMaxC * (kGergMaxC - 1) / 2;
 constexpr int kGergMaxDep = 24;
 constexpr int kGergMaxW = kGergMaxC + kGergMaxDep;
-constexpr int kGergMaxGroup = 64;
-constexpr int kGergMaxTQ = 320;
-constexpr int kGergMaxTerm = 520;
-constexpr int kGergND = 6;  // binomial tables cover derivative orders up to this
+constexpr int kGergMaxGroup = 56;
+constexpr int kGergMaxRec = 800;  // (g,t) headers + terms
+constexpr int kGergND = 6;        // binomial tables cover derivative orders up to this
+constexpr int kGergWS = 128;      // stride between consecutive weights in a thread's column of the staging area (= CTA size)
 
 struct GergRedPair {       // reducing-function data of the pair (i<j), in lexicographic pair order
     double beta2T, YT2;  // beta_T,ij^2 ; 2 * beta_T gamma_T sqrt(Tc_i Tc_j)
@@ -38,69 +42,63 @@ enum GergGroupKind : int { GG_POLY = 0, GG_EXP = 1, GG_GAUSS = 2 };
 struct GergGroup {
     int kind;        // GG_POLY: delta^d ; GG_EXP: delta^d exp(-c delta^l) ; GG_GAUSS: delta^d exp(-eta(delta-eps)^2 - beta(delta-gamma))
     int d, l;        // integer exponents
-    int tq_end;      // one past this group's last entry in tq[]
+    int ntq;         // number of distinct tau exponents in this group
+    int new_h;       // 1: the exponent h(delta) differs from the previous group's -> recompute the Taylor coefficients of exp(h)
+    int pad_[3];
     double c, eta, eps, beta, gamma;
     double bd[kGergND];  // binom(d, m), m = 1..6
     double bl[kGergND];  // binom(l, m), m = 1..6
 };
 
-struct GergTQ {       // a distinct tau exponent inside a group
-    double t;
-    int term_end;    // one past the last term
+// The (g,t) sums are one stream of 16-byte records, read front to back with warp-uniform addresses (one constant load each):
+//   header {val = t, a = number of terms that follow}   then per term   {val = n, a = w * kGergWS}
+struct alignas(16) GergRec {
+    double val;
+    int a;
+    int b_;
 };
 
 struct GergProgram {
-    int nc, nw, ndep, npair, ngroup, ntq, nterm;
-    int pad_;
+    int nc, nw, ndep, npair, ngroup, ntq, nterm, nrec;
     double Tc[kGergMaxC], vc[kGergMaxC];
-    GergRedPair pair[kGergMaxPair];
     double depF[kGergMaxDep];
     unsigned char dep_i[kGergMaxDep], dep_j[kGergMaxDep];
+    GergRedPair pair[kGergMaxPair];
     GergGroup group[kGergMaxGroup];
-    GergTQ tq[kGergMaxTQ];
-    double term_n[kGergMaxTerm];
-    unsigned char term_w[kGergMaxTerm];
+    GergRec rec[kGergMaxRec];
 };
 static_assert(sizeof(GergProgram) <= 32000, "GergProgram must fit in the 32 KB kernel-parameter space");
 
-TQ_HD double ipow(double x, int n) {  // x^n, n >= 0 small (same special cases as teqp::powi, types.hpp:138-170)
-    switch (n) {
-        case 0: return 1.0;
-        case 1: return x;
-        case 2: return x * x;
-        case 3: return x * x * x;
-        case 4: { const double y = x * x; return y * y; }
-    }
-    double y = x, r = 1.0;
-    while (n > 0) {
-        if (n & 1) r *= y;
-        n >>= 1;
-        if (n) y *= y;
-    }
+TQ_HD double ipow(double x, int n) {  // x^n, n >= 0 small: repeated multiplication (n is warp-uniform)
+    double r = 1.0;
+    for (int k = 0; k < n; ++k) r *= x;
     return r;
 }
 
 
-// One state point.  W is this thread's column of the weight staging area (element w at W[w*ws]); on entry W[0..nc) holds the
-// mole fractions.  On exit A[n][m] = tau^n delta^m d^(n+m) alphar / dtau^n ddelta^m / (n! m!).
+// One state point.  W is this thread's column of the weight staging area (element w at W[w*kGergWS]); on entry W[0..nc) holds the
+// mole fractions (WS = kGergWS).  On exit A[n][m] = tau^n delta^m d^(n+m) alphar / dtau^n ddelta^m / (n! m!).
 template<int NT, int ND>
-TQ_HD void gerg_point(const GergProgram& P, const double T, const double rho, double* W, const int ws, double (&A)[NT + 1][ND + 1]) {
-    // ---- reducing functions (GERG.hpp:179-205), same summation order as the reference --------------------------
+TQ_HD void gerg_point(const GergProgram& P, const ExpK& K, const double T, const double rho, double* W, double (&A)[NT + 1][ND + 1]) {
+    // ---- reducing functions (GERG.hpp:179-205), pairs in the reference's order; the two quotients of a pair share one
+    // reciprocal: num/dT = num*dV/(dT*dV).  A pair is skipped when its denominator is zero (x_i = x_j = 0), GERG.hpp:189.
     double s1T = 0.0, s1V = 0.0, s2T = 0.0, s2V = 0.0;
     {
         int pidx = 0;
         for (int i = 0; i < P.nc; ++i) {
-            const double xi = W[i * ws];
+            const double xi = W[i * kGergWS];
             const double xi2 = xi * xi;
-            s1T += xi2 * P.Tc[i];
-            s1V += xi2 * P.vc[i];
+            s1T = fma(xi2, P.Tc[i], s1T);
+            s1V = fma(xi2, P.vc[i], s1V);
             for (int j = i + 1; j < P.nc; ++j, ++pidx) {
-                const double xj = W[j * ws];
-                const double num = xi * xj * (xi + xj);
-                const double dT = P.pair[pidx].beta2T * xi + xj;
-                const double dV = P.pair[pidx].beta2V * xi + xj;
-                if (dT != 0.0) s2T += num / dT * P.pair[pidx].YT2;
-                if (dV != 0.0) s2V += num / dV * P.pair[pidx].YV2;
+                const double xj = W[j * kGergWS];
+                const GergRedPair pr = P.pair[pidx];
+                const double dT = fma(pr.beta2T, xi, xj);
+                const double dV = fma(pr.beta2V, xi, xj);
+                const double den = dT * dV;
+                const double q = (xi * xj) * (xi + xj) * fast_rcp(den != 0.0 ? den : 1.0);  // numerator is 0 whenever den is
+                s2T = fma(q * dV, pr.YT2, s2T);
+                s2V = fma(q * dT, pr.YV2, s2V);
             }
         }
     }
@@ -109,7 +107,7 @@ TQ_HD void gerg_point(const GergProgram& P, const double T, const double rho, do
     const double tau = Tr / T;
     const double delta = rho * Yv;
     const double lntau = log(tau);
-    for (int q = 0; q < P.ndep; ++q) W[(P.nc + q) * ws] = W[P.dep_i[q] * ws] * W[P.dep_j[q] * ws] * P.depF[q];
+    for (int q = 0; q < P.ndep; ++q) W[(P.nc + q) * kGergWS] = W[P.dep_i[q] * kGergWS] * W[P.dep_j[q] * kGergWS] * P.depF[q];
 
     // ---- factorised term sum ------------------------------------------------------------------------------------
 #pragma unroll
@@ -117,19 +115,18 @@ TQ_HD void gerg_point(const GergProgram& P, const double T, const double rho, do
 #pragma unroll
         for (int m = 0; m <= ND; ++m) A[n][m] = 0.0;
 
-    int tq = 0, term = 0;
+    int rec = 0;
+    double E[ND + 1];   // delta^m/m! d^m/ddelta^m exp(h(delta)), shared by consecutive groups with the same h
+    double dd = 1.0;    // running delta^dcur
+    int dcur = 0;
     for (int g = 0; g < P.ngroup; ++g) {
         const GergGroup& gr = P.group[g];
-        // G[m] = delta^m/m! d^m/ddelta^m [ delta^d exp(h(delta)) ]
-        double G[ND + 1];
-        const double dd = ipow(delta, gr.d);
-        if (gr.kind == GG_POLY) {
-            G[0] = dd;
-#pragma unroll
-            for (int m = 1; m <= ND; ++m) G[m] = gr.bd[m - 1] * dd;
-        } else {
+        if (gr.new_h) {
             double h[ND + 1];
-            if (gr.kind == GG_EXP) {
+            if (gr.kind == GG_POLY) {
+#pragma unroll
+                for (int m = 0; m <= ND; ++m) h[m] = 0.0;
+            } else if (gr.kind == GG_EXP) {
                 const double cdl = -gr.c * ipow(delta, gr.l);
                 h[0] = cdl;
 #pragma unroll
@@ -142,38 +139,49 @@ TQ_HD void gerg_point(const GergProgram& P, const double T, const double rho, do
 #pragma unroll
                 for (int m = 3; m <= ND; ++m) h[m] = 0.0;
             }
-            double E[ND + 1];
-            E[0] = exp(h[0]);
+            E[0] = (gr.kind == GG_POLY) ? 1.0 : fast_exp(h[0], K);
 #pragma unroll
             for (int m = 1; m <= ND; ++m) {
                 double s = h[1 <= ND ? 1 : 0] * E[m - 1];
 #pragma unroll
-                for (int j = 2; j <= m; ++j) s += (double(j) * h[j]) * E[m - j];
+                for (int j = 2; j <= m; ++j) s = fma(double(j) * h[j], E[m - j], s);
                 E[m] = s * (1.0 / double(m));
             }
+            dd = 1.0;
+            dcur = 0;
+        }
+        for (; dcur < gr.d; ++dcur) dd *= delta;
+        // G[m] = delta^m/m! d^m/ddelta^m [ delta^d exp(h(delta)) ] = delta^d sum_j binom(d,j) E[m-j]
+        double G[ND + 1];
 #pragma unroll
-            for (int m = 0; m <= ND; ++m) {
-                double s = E[m];  // binom(d,0) = 1
+        for (int m = 0; m <= ND; ++m) {
+            double s = E[m];
 #pragma unroll
-                for (int j = 1; j <= m; ++j) s += gr.bd[j - 1] * E[m - j];
-                G[m] = s * dd;
-            }
+            for (int j = 1; j <= m; ++j) s = fma(gr.bd[j - 1], E[m - j], s);
+            G[m] = s * dd;
         }
         // C[n] = tau^n/n! d^n/dtau^n sum_t c_t tau^t
         double C[NT + 1];
 #pragma unroll
         for (int n = 0; n <= NT; ++n) C[n] = 0.0;
-        const int tq_end = gr.tq_end;
-        for (; tq < tq_end; ++tq) {
-            const double t = P.tq[tq].t;
-            const int term_end = P.tq[tq].term_end;
+        for (int q = 0; q < gr.ntq; ++q) {
+            const GergRec hd = P.rec[rec++];
+            const double t = hd.val;
+            const double e = fast_exp(t * lntau, K);
             double c0 = 0.0, c1 = 0.0;
-            for (; term + 1 < term_end; term += 2) {
-                c0 = fma(W[P.term_w[term] * ws], P.term_n[term], c0);
-                c1 = fma(W[P.term_w[term + 1] * ws], P.term_n[term + 1], c1);
+            int k = 0;
+#pragma unroll 1
+            for (; k + 1 < hd.a; k += 2) {
+                const GergRec r0 = P.rec[rec], r1 = P.rec[rec + 1];
+                rec += 2;
+                c0 = fma(W[r0.a], r0.val, c0);
+                c1 = fma(W[r1.a], r1.val, c1);
             }
-            if (term < term_end) { c0 = fma(W[P.term_w[term] * ws], P.term_n[term], c0); ++term; }
-            double v = (c0 + c1) * exp(t * lntau);
+            if (k < hd.a) {
+                const GergRec r0 = P.rec[rec++];
+                c0 = fma(W[r0.a], r0.val, c0);
+            }
+            double v = (c0 + c1) * e;
             C[0] += v;
 #pragma unroll
             for (int n = 1; n <= NT; ++n) {

@@ -21,11 +21,12 @@ void put(const std::string& m, char* e, int n) { if (e && n > 0) { std::strncpy(
 
 template<int NT, int ND>
 void gerg_loop(const GergProgram& P, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
-    std::vector<double> W(P.nw);
+    const ExpK K = ExpK::load();
+    std::vector<double> W((size_t)P.nw * kGergWS);  // same column stride as a CTA's staging area; column 0 is used
     for (long long k = 0; k < npts; ++k) {
-        for (int i = 0; i < P.nc; ++i) W[i] = x[(long long)i * xs + (xs ? k : 0)];
+        for (int i = 0; i < P.nc; ++i) W[(size_t)i * kGergWS] = x[(long long)i * xs + (xs ? k : 0)];
         double A[NT + 1][ND + 1];
-        gerg_point<NT, ND>(P, T[k], rho[k], W.data(), 1, A);
+        gerg_point<NT, ND>(P, K, T[k], rho[k], W.data(), A);
         double fn = 1;
         for (int n = 0; n <= NT; ++n) {
             if (n >= 2) fn *= n;
