@@ -2,6 +2,7 @@
 // See tq_gerg.cuh for the factorisation.  Reference factories: /root/reference/interface/CPP/model_factory_GERG.cpp:13-18,
 // model classes /root/reference/include/teqp/models/GERG/GERG.hpp:902-937 (2004) and :1166-1202 (2008).
 #include <algorithm>
+#include <cmath>
 #include <cctype>
 #include <map>
 #include <tuple>
@@ -38,7 +39,7 @@ __global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_cons
                                                                double* __restrict__ out) {
     extern __shared__ double Wsh[];  // [nw][kBlock]; each thread touches only its own column -> no barriers needed
     double* W = Wsh + threadIdx.x;
-    const ExpK K = ExpK::load(in.npts >> 62);  // npts < 2^62: the shift is 0, but only at run time
+    const Exp2K K = Exp2K::load(in.npts >> 62);  // npts < 2^62: the shift is 0, but only at run time
     const long long npts = in.npts;
     const long long stride = (long long)gridDim.x * kBlock;
     for (long long k = (long long)blockIdx.x * kBlock + threadIdx.x; k < npts; k += stride) {
@@ -95,7 +96,10 @@ public:
     template<int NT, int ND> void launch(const DeviceBatch& in, double* out, cudaStream_t st) const {
         const size_t smem = (size_t)P.nw * kBlock * sizeof(double);
         static_assert(kGergMaxW * kBlock * sizeof(double) <= 48 * 1024, "W staging must fit the default 48 KB dynamic shared memory");
-        const int grid = grid_for(in.npts, kBlock, sm_count() * 8);
+        // persistent grid: exactly as many CTAs as are resident at once (occupancy x SMs), each striding over the batch
+        int occ = 1;
+        TQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gerg_ar_table_kernel<NT, ND>, kBlock, smem));
+        const int grid = grid_for(in.npts, kBlock, sm_count() * (occ > 0 ? occ : 1));
         gerg_ar_table_kernel<NT, ND><<<grid, kBlock, smem, st>>>(P, in, out);
         TQ_CUDA(cudaGetLastError());
     }
@@ -200,9 +204,15 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
         G.ntq = (int)bytau.size();
         for (const auto& [t, terms] : bytau) {
-            if (rec + 1 + (int)terms.size() > kGergMaxRec) throw InvalidArgument("too many terms for the device term program");
-            P.rec[rec].val = t; P.rec[rec].a = (int)terms.size(); ++rec;
-            for (const RawTerm* r : terms) { P.rec[rec].val = r->n; P.rec[rec].a = r->w * kGergWS; ++rec; ++term; }
+            const int rest = (int)terms.size() - 1, npair = (rest + 1) / 2;
+            if (rec + 2 + 2 * npair > kGergMaxRec) throw InvalidArgument("too many terms for the device term program");
+            if (!(std::fabs(t) <= kGergMaxAbsT)) throw InvalidArgument("temperature exponent out of the device term program's range");
+            P.rec[rec] = GergRec{t, npair, terms[0]->w * kGergWS * 8};
+            P.rec[rec + 1] = GergRec{terms[0]->n, 0, 0};
+            rec += 2;
+            for (int k = 0; k < 2 * npair; ++k, ++rec)
+                P.rec[rec] = (k < rest) ? GergRec{terms[k + 1]->n, terms[k + 1]->w * kGergWS * 8, 0} : GergRec{0.0, 0, 0};
+            term += (int)terms.size();
             ++tq;
         }
         ++g;

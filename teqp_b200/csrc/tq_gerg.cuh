@@ -50,12 +50,15 @@ struct GergGroup {
     double bl[kGergND];  // binom(l, m), m = 1..6
 };
 
-// The (g,t) sums are one stream of 16-byte records, read front to back with warp-uniform addresses (one constant load each):
-//   header {val = t, a = number of terms that follow}   then per term   {val = n, a = w * kGergWS}
+// The (g,t) sums are one stream of 16-byte units, read front to back with warp-uniform addresses:
+//   (g,t) header, 2 units: {val = t, a = number of term PAIRS that follow, b = byte offset of the first term's weight}
+//                          {val = n of the first term}
+//   then per further term  {val = n, a = byte offset of its weight}, padded with {0, 0} to an even count
+// (62 of the 109 (g,t) sums of the 10-component natural gas have a single term: no inner loop for those)
 struct alignas(16) GergRec {
     double val;
     int a;
-    int b_;
+    int b;
 };
 
 struct GergProgram {
@@ -69,6 +72,11 @@ struct GergProgram {
 };
 static_assert(sizeof(GergProgram) <= 32000, "GergProgram must fit in the 32 KB kernel-parameter space");
 
+TQ_HD double wload(const double* W, int byte_offset) {
+    return *reinterpret_cast<const double*>(reinterpret_cast<const char*>(W) + byte_offset);
+}
+constexpr double kGergMaxAbsT = 30.0;  // largest |t| the device term program accepts (GERG-2008: 30)
+
 TQ_HD double ipow(double x, int n) {  // x^n, n >= 0 small: repeated multiplication (n is warp-uniform)
     double r = 1.0;
     for (int k = 0; k < n; ++k) r *= x;
@@ -79,7 +87,7 @@ TQ_HD double ipow(double x, int n) {  // x^n, n >= 0 small: repeated multiplicat
 // One state point.  W is this thread's column of the weight staging area (element w at W[w*kGergWS]); on entry W[0..nc) holds the
 // mole fractions (WS = kGergWS).  On exit A[n][m] = tau^n delta^m d^(n+m) alphar / dtau^n ddelta^m / (n! m!).
 template<int NT, int ND>
-TQ_HD void gerg_point(const GergProgram& P, const ExpK& K, const double T, const double rho, double* W, double (&A)[NT + 1][ND + 1]) {
+TQ_HD void gerg_point(const GergProgram& P, const Exp2K& K, const double T, const double rho, double* W, double (&A)[NT + 1][ND + 1]) {
     // ---- reducing functions (GERG.hpp:179-205), pairs in the reference's order; the two quotients of a pair share one
     // reciprocal: num/dT = num*dV/(dT*dV).  A pair is skipped when its denominator is zero (x_i = x_j = 0), GERG.hpp:189.
     double s1T = 0.0, s1V = 0.0, s2T = 0.0, s2V = 0.0;
@@ -106,14 +114,19 @@ TQ_HD void gerg_point(const GergProgram& P, const ExpK& K, const double T, const
     const double Yv = s1V + s2V;  // 1/rho_r
     const double tau = Tr / T;
     const double delta = rho * Yv;
-    const double lntau = log(tau);
+    // tau^t = 2^(t log2 tau); |t| <= kGergMaxAbsT is checked when the program is built, log2 tau is clamped so that the
+    // product stays inside fast_exp2_bounded's range.  nanfix turns a non-finite log2 tau (T <= 0, NaN) into NaN results.
+    double l2tau = log2(tau);
+    const double nanfix = l2tau - l2tau;
+    l2tau = (l2tau > 30.0) ? 30.0 : l2tau;
+    l2tau = (l2tau < -30.0) ? -30.0 : l2tau;
     for (int q = 0; q < P.ndep; ++q) W[(P.nc + q) * kGergWS] = W[P.dep_i[q] * kGergWS] * W[P.dep_j[q] * kGergWS] * P.depF[q];
 
     // ---- factorised term sum ------------------------------------------------------------------------------------
 #pragma unroll
     for (int n = 0; n <= NT; ++n)
 #pragma unroll
-        for (int m = 0; m <= ND; ++m) A[n][m] = 0.0;
+        for (int m = 0; m <= ND; ++m) A[n][m] = nanfix;
 
     int rec = 0;
     double E[ND + 1];   // delta^m/m! d^m/ddelta^m exp(h(delta)), shared by consecutive groups with the same h
@@ -139,7 +152,7 @@ TQ_HD void gerg_point(const GergProgram& P, const ExpK& K, const double T, const
 #pragma unroll
                 for (int m = 3; m <= ND; ++m) h[m] = 0.0;
             }
-            E[0] = (gr.kind == GG_POLY) ? 1.0 : fast_exp(h[0], K);
+            E[0] = (gr.kind == GG_POLY) ? 1.0 : fast_exp(h[0]);
 #pragma unroll
             for (int m = 1; m <= ND; ++m) {
                 double s = h[1 <= ND ? 1 : 0] * E[m - 1];
@@ -165,23 +178,20 @@ TQ_HD void gerg_point(const GergProgram& P, const ExpK& K, const double T, const
 #pragma unroll
         for (int n = 0; n <= NT; ++n) C[n] = 0.0;
         for (int q = 0; q < gr.ntq; ++q) {
-            const GergRec hd = P.rec[rec++];
+            const GergRec hd = P.rec[rec];
+            const double n0 = P.rec[rec + 1].val;
+            rec += 2;
             const double t = hd.val;
-            const double e = fast_exp(t * lntau, K);
-            double c0 = 0.0, c1 = 0.0;
-            int k = 0;
+            const double e = fast_exp2_bounded(t * l2tau, K);
+            double c = wload(W, hd.b) * n0;
 #pragma unroll 1
-            for (; k + 1 < hd.a; k += 2) {
+            for (int k = 0; k < hd.a; ++k) {
                 const GergRec r0 = P.rec[rec], r1 = P.rec[rec + 1];
                 rec += 2;
-                c0 = fma(W[r0.a], r0.val, c0);
-                c1 = fma(W[r1.a], r1.val, c1);
+                c = fma(wload(W, r0.a), r0.val, c);
+                c = fma(wload(W, r1.a), r1.val, c);
             }
-            if (k < hd.a) {
-                const GergRec r0 = P.rec[rec++];
-                c0 = fma(W[r0.a], r0.val, c0);
-            }
-            double v = (c0 + c1) * e;
+            double v = c * e;
             C[0] += v;
 #pragma unroll
             for (int n = 1; n <= NT; ++n) {

@@ -45,47 +45,69 @@ TQ_HD int bits_lo32(double t) {
 #define TQ_EXP_COEFFS                                                                                                   \
     { 0x1.71547652b82fep+0, 0x1.62e42fefa39efp-1, 0x1.abc9e3b39803fp-56, 0x1.af38a9b0ec855p-26, 0x1.289185613a3d6p-22,  \
       0x1.71de0dae63bb3p-19, 0x1.a019b90d2ae7ap-16, 0x1.a01a01a7c41d5p-13, 0x1.6c16c1788bd90p-10, 0x1.11111111109b3p-7, \
-      0x1.5555555553d63p-5, 0x1.5555555555556p-3, 0x1.0000000000001p-1, 0x1.8p+52, -708.0, 709.0 }
+      0x1.5555555553d63p-5, 0x1.5555555555556p-3, 0x1.0000000000001p-1, 0x1.8p+52, -708.0, 709.0,                      \
+      /* [16..26]: 2^r = 1 + c1 r + .. + c11 r^11, |r| <= 1/2 (same fit, tools/fit_exp_poly.py) */                    \
+      0x1.62e42fefa39efp-1, 0x1.ebfbdff82c590p-3, 0x1.c6b08d704a0c0p-5, 0x1.3b2ab6fba385bp-7, 0x1.5d87fe78a5dc3p-10,  \
+      0x1.4309130379f8bp-13, 0x1.ffcbfc61f8673p-17, 0x1.62bfe45ac08ccp-20, 0x1.b525087314718p-24,                      \
+      0x1.e5ea03c5ae3ccp-28, 0x1.e9bbe9e45e5a6p-32, 0.0, 0.0, 0.0, 0.0, 0.0 }
 #if defined(__CUDACC__)
-static __constant__ double kExpC_dev[16] = TQ_EXP_COEFFS;
+static __constant__ double kExpC_dev[32] = TQ_EXP_COEFFS;
 #endif
-static const double kExpC_host[16] = TQ_EXP_COEFFS;
+static const double kExpC_host[32] = TQ_EXP_COEFFS;
 
-// The coefficients as a value type: a kernel loads it ONCE into registers (ExpK::load) and passes it down, so the
-// polynomial's operands are registers instead of ~9 constant loads per call.
-struct ExpK {
-    double k[16];
-    // opaque_zero: any run-time value that is 0 but that the compiler cannot prove to be 0.  With a compile-time-known
-    // address ptxas re-materialises the constant loads before every use (9 loads per exp); an address it cannot fold keeps
-    // the 13 coefficients resident in (uniform) registers for the whole kernel.
-    TQ_HD static ExpK load(long long opaque_zero = 0) {
-        ExpK r;
+// exp(x), coefficients read from constant memory at the point of use (fine for the few calls per state point that need the
+// full argument range; the hot 2^y below keeps its coefficients in registers instead)
+TQ_HD double fast_exp(double x) {
 #if defined(__CUDA_ARCH__)
-        const size_t base = __cvta_generic_to_constant(kExpC_dev) + (size_t)opaque_zero;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) asm volatile("ld.const.f64 %0, [%1];" : "=d"(r.k[i]) : "l"(base + 8 * i));
+    const double* K = kExpC_dev;
 #else
-        for (int i = 0; i < 16; ++i) r.k[i] = kExpC_host[i];
+    const double* K = kExpC_host;
 #endif
-        return r;
-    }
-};
-
-TQ_HD double fast_exp(double x, const ExpK& K) {
     const double xc = (x < -708.0) ? -708.0 : x;
-    const double t = fma(xc, K.k[0], 0x1.8p+52);  // x/ln2 rounded to nearest integer, in the low mantissa bits
+    const double t = fma(xc, K[0], 0x1.8p+52);  // x/ln2 rounded to nearest integer, in the low mantissa bits
     const double nf = t - 0x1.8p+52;
-    double r = fma(-nf, K.k[1], xc);
-    r = fma(-nf, K.k[2], r);
-    double p = K.k[3];
+    double r = fma(-nf, K[1], xc);
+    r = fma(-nf, K[2], r);
+    double p = K[3];
 #pragma unroll
-    for (int k = 4; k <= 12; ++k) p = fma(p, r, K.k[k]);
+    for (int k = 4; k <= 12; ++k) p = fma(p, r, K[k]);
     p = fma(p, r, 1.0);
     p = fma(p, r, 1.0);
     p = bits_add_exponent(p, bits_lo32(t));
     return (x > 709.0) ? INFINITY : p;
 }
-TQ_HD double fast_exp(double x) { return fast_exp(x, ExpK::load()); }
+
+// The 2^r coefficients as a value type: a kernel loads it ONCE (Exp2K::load) and passes it down, so that the polynomial's
+// operands stay resident in (uniform) registers instead of being re-loaded from constant memory before every use.
+struct Exp2K {
+    double c[11];
+    // opaque_zero: any run-time value that is 0 but that the compiler cannot prove to be 0.  With a compile-time-known
+    // address ptxas re-materialises the constant loads before every use (~6 loads per call); an address it cannot fold
+    // keeps the coefficients in registers for the whole kernel.
+    TQ_HD static Exp2K load(long long opaque_zero = 0) {
+        Exp2K r;
+#if defined(__CUDA_ARCH__)
+        const size_t base = __cvta_generic_to_constant(kExpC_dev + 16) + (size_t)opaque_zero;
+#pragma unroll
+        for (int i = 0; i < 11; ++i) asm volatile("ld.const.f64 %0, [%1];" : "=d"(r.c[i]) : "l"(base + 8 * i));
+#else
+        for (int i = 0; i < 11; ++i) r.c[i] = kExpC_host[16 + i];
+#endif
+        return r;
+    }
+};
+
+// 2^y for |y| < 1000 (NOT checked: the caller bounds its argument).  r = y - rint(y) is exact, so the whole error is the
+// polynomial's (1.7e-17) plus Horner rounding: <= 1 ulp.  14 FP64 instructions, no branches.
+TQ_HD double fast_exp2_bounded(double y, const Exp2K& K) {
+    const double t = y + 0x1.8p+52;
+    const double r = y - (t - 0x1.8p+52);
+    double p = K.c[10];
+#pragma unroll
+    for (int k = 9; k >= 0; --k) p = fma(p, r, K.c[k]);
+    p = fma(p, r, 1.0);
+    return bits_add_exponent(p, bits_lo32(t));
+}
 
 // 1/a for a normal, finite, non-zero a (the callers guard zero): hardware seed + two Newton steps, <= 1 ulp
 TQ_HD double fast_rcp(double a) {

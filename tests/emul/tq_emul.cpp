@@ -21,7 +21,7 @@ void put(const std::string& m, char* e, int n) { if (e && n > 0) { std::strncpy(
 
 template<int NT, int ND>
 void gerg_loop(const GergProgram& P, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
-    const ExpK K = ExpK::load();
+    const Exp2K K = Exp2K::load();
     std::vector<double> W((size_t)P.nw * kGergWS);  // same column stride as a CTA's staging area; column 0 is used
     for (long long k = 0; k < npts; ++k) {
         for (int i = 0; i < P.nc; ++i) W[(size_t)i * kGergWS] = x[(long long)i * xs + (xs ? k : 0)];

@@ -54,3 +54,23 @@ ref = np.array([float(mp.exp(mp.mpf(float(v)))) for v in x[::50]])
 rel = np.abs(got[::50] - ref) / ref
 print("double evaluation (unfused numpy): max rel err %.3e = %.2f ulp, mean %.2e" % (rel.max(), rel.max() / 2.2e-16, rel.mean()))
 print("max |r|", np.abs(r).max())
+
+# ---- the same for 2^r on |r| <= 1/2 (tq::fast_exp2): 2^r ~ 1 + r (ln2 + r q2(r)), coefficients of degree 1..DEG
+B = mp.mpf("0.5") * mp.mpf("1.0001")
+LN2 = mp.log(2)
+nq2 = DEG - 1
+f2 = lambda r: (mp.power(2, r) - 1 - r * LN2) / (r * r) if abs(r) > mp.mpf("1e-25") else LN2 ** 2 / 2
+xs = [B * mp.cos(mp.pi * (2 * k + 1) / (2 * nq2)) for k in range(nq2)]
+M = mp.matrix(nq2, nq2); b = mp.matrix(nq2, 1)
+for i, x in enumerate(xs):
+    for j in range(nq2):
+        M[i, j] = x ** j
+    b[i] = f2(x)
+sol = mp.lu_solve(M, b)
+c2 = [sol[j] for j in range(nq2)]
+grid = [-B + 2 * B * mp.mpf(k) / 2000 for k in range(2001)]
+mx2 = max(abs((f2(x) - sum(c2[j] * x ** j for j in range(nq2))) * x * x / mp.power(2, x)) for x in grid)
+print("exp2 degree", DEG, "max relative error (exact coefficients) %.3e" % float(mx2))
+coef2 = [1.0, float(LN2)] + [float(cj) for cj in c2]
+print("exp2 coefficients c1..c%d:" % DEG)
+print(", ".join(v.hex() for v in coef2[1:]))
