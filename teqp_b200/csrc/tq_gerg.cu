@@ -96,10 +96,10 @@ public:
     template<int NT, int ND> void launch(const DeviceBatch& in, double* out, cudaStream_t st) const {
         const size_t smem = (size_t)P.nw * kBlock * sizeof(double);
         static_assert(kGergMaxW * kBlock * sizeof(double) <= 48 * 1024, "W staging must fit the default 48 KB dynamic shared memory");
-        // persistent grid: exactly as many CTAs as are resident at once (occupancy x SMs), each striding over the batch
-        int occ = 1;
-        TQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gerg_ar_table_kernel<NT, ND>, kBlock, smem));
-        const int grid = grid_for(in.npts, kBlock, sm_count() * (occ > 0 ? occ : 1));
+        // one state point per thread, one CTA per 128 points: with ~11 000 instructions per point the CTA launch cost is noise,
+        // and the hardware CTA scheduler balances the SMs (a persistent grid-stride grid left 30 % of the warp slots idle in
+        // its tail: profiles/r01c)
+        const int grid = grid_for(in.npts, kBlock, 1 << 30);
         gerg_ar_table_kernel<NT, ND><<<grid, kBlock, smem, st>>>(P, in, out);
         TQ_CUDA(cudaGetLastError());
     }
