@@ -9,6 +9,7 @@
 
 #include "tq_common.hpp"
 #include "tq_gerg.cuh"
+#include "tq_gerg_iso.cuh"
 
 namespace tq {
 
@@ -93,6 +94,9 @@ public:
     double R(const double*, int) const override { return Rgas; }
     const void* params_blob(size_t* n) const override { *n = sizeof(P); return &P; }
 
+    void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
+        gerg_launch_isochoric(P, Rgas, in, o, st);
+    }
     template<int NT, int ND> void launch(const DeviceBatch& in, double* out, cudaStream_t st) const {
         const size_t smem = (size_t)P.nw * kBlock * sizeof(double);
         static_assert(kGergMaxW * kBlock * sizeof(double) <= 48 * 1024, "W staging must fit the default 48 KB dynamic shared memory");

@@ -12,6 +12,7 @@
 #include "../../teqp_b200/csrc/tq_cubic.cuh"
 #include "../../teqp_b200/csrc/tq_generic.cuh"
 #include "../../teqp_b200/csrc/tq_gerg.cuh"
+#include "../../teqp_b200/csrc/tq_gerg_iso.cuh"
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
 
 using namespace tq;
@@ -75,6 +76,16 @@ void generic_iso(const typename M::Params& p, int nc, long long npts, const doub
         double r[M::kMaxC];
         for (int i = 0; i < nc; ++i) r[i] = rv[(long long)i * npts + k];
         generic_isochoric_point<M, M::kMaxC>(p, nc, T[k], r, o, k, npts);
+    }
+}
+void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const double* T, const double* rv, const IsochoricOut& o) {
+    constexpr int WS = 32;
+    const Exp2K K = Exp2K::load();
+    std::vector<double> W((size_t)gerg_iso_rows(P.nc, P.nw, true) * WS);
+    for (long long k = 0; k < npts; ++k) {
+        for (int i = 0; i < P.nc; ++i) W[(size_t)i * WS] = rv[(long long)i * npts + k];
+        if (o.hess) gerg_iso_point<WS, true>(P, K, Rgas, T[k], W.data(), o, k, npts);
+        else gerg_iso_point<WS, false>(P, K, Rgas, T[k], W.data(), o, k, npts);
     }
 }
 }  // namespace
@@ -143,6 +154,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         IsochoricOut o; o.Psir = f; o.grad = g; o.hess = H; o.lnphi = lnphi; o.phi = phi;
         if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam.rfind("GERG", 0) == 0) gerg_iso_loop(*static_cast<const GergProgram*>(blob), m->R(nullptr, 0), npts, T, rhovec, o);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }

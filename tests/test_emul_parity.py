@@ -17,7 +17,7 @@ def test_atrhoxi(emul, oracle, name):
     ps.atrhoxi(ps.EmulBackend(emul), oracle, name, n=200)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
 def test_isochoric(emul, oracle, name):
     ps.isochoric(ps.EmulBackend(emul), oracle, name, n=300)
 

@@ -32,7 +32,7 @@ def test_atrhoxi(be, oracle, name):
     ps.atrhoxi(be, oracle, name, n=400)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
 def test_isochoric(be, oracle, name):
     ps.isochoric(be, oracle, name, n=600)
 
