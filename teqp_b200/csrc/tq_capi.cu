@@ -33,6 +33,8 @@ std::unique_ptr<Model> make_model(const Json& j) {
     if (kind == "PR" || kind == "SRK" || kind == "cubic") return make_cubic_model(kind, spec);
     if (kind == "GERG2008resid" || kind == "GERG2004resid") return make_gerg_model(kind, spec);
     if (kind == "PCSAFT") return make_pcsaft_model(spec);
+    if (kind == "SAFT-VR-Mie") return make_saftvrmie_model(spec);
+    if (kind == "genericSAFT") return make_genericsaft_model(spec);
     throw InvalidArgument("Don't understand \"kind\" of: " + kind);
 }
 

@@ -91,6 +91,8 @@ std::unique_ptr<Model> make_cubic_model(const std::string& kind, const Json& spe
 std::unique_ptr<Model> make_vdw_model(const std::string& kind, const Json& spec);
 std::unique_ptr<Model> make_gerg_model(const std::string& kind, const Json& spec);
 std::unique_ptr<Model> make_pcsaft_model(const Json& spec);
+std::unique_ptr<Model> make_saftvrmie_model(const Json& spec);
+std::unique_ptr<Model> make_genericsaft_model(const Json& spec);
 std::unique_ptr<Model> make_model(const Json& j);
 
 inline int grid_for(long long npts, int block, int max_blocks) {

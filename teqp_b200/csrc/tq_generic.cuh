@@ -18,6 +18,11 @@
 
 namespace tq {
 
+// A family that declares `static constexpr bool kNoSmallVariants = true` gets ONE kernel variant per jet shape (arrays sized
+// kMaxC, component count at run time) instead of the four specialised for 1, 2, 3 and kMaxC components.
+template<class M, class = void> struct small_variants : std::true_type {};
+template<class M> struct small_variants<M, std::void_t<decltype(M::kNoSmallVariants)>> : std::false_type {};
+
 // ------------------------------------------------------------------------------------------------------------------
 // Lambda^r_nm table
 // ------------------------------------------------------------------------------------------------------------------
@@ -73,10 +78,14 @@ template<class M, int CT, int CD>
 void generic_launch_ar_table_inst(const typename M::Params& p, int nc, int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) {
     const int block = 128;
     const int grid = grid_for(in.npts, block, sm_count() * 32);
-    if (nc == 1) generic_ar_table_kernel<M, 1, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
-    else if (nc == 2) generic_ar_table_kernel<M, 2, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
-    else if (nc == 3) generic_ar_table_kernel<M, 3, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
-    else generic_ar_table_kernel<M, M::kMaxC, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    if constexpr (small_variants<M>::value) {
+        if (nc == 1) generic_ar_table_kernel<M, 1, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+        else if (nc == 2) generic_ar_table_kernel<M, 2, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+        else if (nc == 3) generic_ar_table_kernel<M, 3, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+        else generic_ar_table_kernel<M, M::kMaxC, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    } else {
+        generic_ar_table_kernel<M, M::kMaxC, CT, CD><<<grid, block, 0, st>>>(p, nc, in, NT, ND, out);
+    }
     TQ_CUDA(cudaGetLastError());
 }
 
@@ -167,10 +176,14 @@ void generic_launch_ATrhoXi(const typename M::Params& p, int nc, const DeviceBat
     if (in.npts == 0) return;
     const int block = 64;
     const int grid = grid_for(in.npts, block, sm_count() * 32);
-    if (nc == 1) generic_ATrhoXi_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, out);
-    else if (nc == 2) generic_ATrhoXi_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, out);
-    else if (nc == 3) generic_ATrhoXi_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, out);
-    else generic_ATrhoXi_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, out);
+    if constexpr (small_variants<M>::value) {
+        if (nc == 1) generic_ATrhoXi_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, out);
+        else if (nc == 2) generic_ATrhoXi_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, out);
+        else if (nc == 3) generic_ATrhoXi_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, out);
+        else generic_ATrhoXi_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, out);
+    } else {
+        generic_ATrhoXi_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, out);
+    }
     TQ_CUDA(cudaGetLastError());
 }
 
@@ -273,10 +286,14 @@ void generic_launch_isochoric(const typename M::Params& p, int nc, const DeviceB
     if (in.npts == 0) return;
     const int block = 64;
     const int grid = grid_for(in.npts, block, sm_count() * 32);
-    if (nc == 1) generic_isochoric_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, o);
-    else if (nc == 2) generic_isochoric_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, o);
-    else if (nc == 3) generic_isochoric_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, o);
-    else generic_isochoric_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, o);
+    if constexpr (small_variants<M>::value) {
+        if (nc == 1) generic_isochoric_kernel<M, 1><<<grid, block, 0, st>>>(p, nc, in, o);
+        else if (nc == 2) generic_isochoric_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, o);
+        else if (nc == 3) generic_isochoric_kernel<M, 3><<<grid, block, 0, st>>>(p, nc, in, o);
+        else generic_isochoric_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, o);
+    } else {
+        generic_isochoric_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, o);
+    }
     TQ_CUDA(cudaGetLastError());
 }
 

@@ -46,6 +46,26 @@ _GERG21 = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "n-butan
            "n-heptane", "n-octane", "hydrogen", "oxygen", "carbonmonoxide", "water", "helium", "argon", "hydrogensulfide", "n-nonane", "n-decane"]
 
 
+# C4: methane + ethane (library values) + water (Dufal-2015 values, src/tests/catch_test_SAFTgeneric.cxx:104-128) + methane + ethane (library values,
+# include/teqp/models/saftvrmie.hpp:51-52).  Only water carries association sites, and it is the LAST component: the reference reads
+# the Dufal pair tables of (i, j) as those of (i, N-1), so with water anywhere else its own association
+# would be evaluated with epsilon_HB(water, last) = 0 and vanish
+_C4_SPEC = {"kind": "genericSAFT", "model": {
+    "nonpolar": {"kind": "SAFT-VR-Mie", "model": {"coeffs": [
+        {"name": "Methane", "BibTeXKey": "Lafitte-JCP-2001", "m": 1.0, "sigma_Angstrom": 3.7412, "epsilon_over_k": 153.36, "lambda_r": 12.650, "lambda_a": 6.0},
+        {"name": "Ethane", "BibTeXKey": "Lafitte-JCP-2001", "m": 1.4373, "sigma_Angstrom": 3.7257, "epsilon_over_k": 206.12, "lambda_r": 12.400, "lambda_a": 6.0},
+        {"name": "Water", "BibTeXKey": "Dufal-2015", "m": 1.0, "sigma_Angstrom": 3.0555, "epsilon_over_k": 418.00, "lambda_r": 35.823, "lambda_a": 6.0}]}},
+    "association": {"kind": "Dufal", "model": {
+        "sigma / m": [3.7412e-10, 3.7257e-10, 3.0555e-10],
+        "epsilon / J/mol": [1275.1063705805507, 1713.7770350136118, 3475.445374388054],
+        "lambda_r": [12.650, 12.400, 35.823],
+        "epsilon_HB / J/mol": [0.0, 0.0, 13303.140189045183],
+        "K_HB / m^3": [0.0, 0.0, 496.66e-30],
+        "kmat": [[0.0, 0.0, 0.0], [0.0, 0.0, 0.0], [0.0, 0.0, 0.0]],
+        "Delta_rule": "Dufal",
+        "molecule_sites": [[], [], ["e", "e", "H", "H"]]}}}}
+
+
 def _norm(z):
     z = np.asarray(z, dtype=np.float64)
     return (z / z.sum()).tolist()
@@ -61,6 +81,8 @@ WORKLOADS = {
     # C3: GERG-2008 10-component natural gas, Ar00..Ar04 -- the headline
     "C3": dict(spec={"kind": "GERG2008resid", "model": {"names": _C3_NAMES}},
                T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm(_C3_Z), npts=10**8, what="Ar0n", nmax=4, bytes_per_point=136),
+    # C4: SAFT-VR-Mie ternary with Dufal association on water: the get_ATrhoXi table (23 combinations x 3 components)
+    "C4": dict(spec=_C4_SPEC, T=(280.0, 500.0), rho=(10.0, 30000.0), z0=[0.3, 0.3, 0.4], npts=10**7, what="ATrhoXi", bytes_per_point=40 + 8 * 108),
     # C5 (Ar0n variant): GERG-2008 all 21 components
     "C5": dict(spec={"kind": "GERG2008resid", "model": {"names": _GERG21}},
                T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm([1.0] * 21), npts=10**6, what="Ar0n", nmax=4, bytes_per_point=224),

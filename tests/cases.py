@@ -22,6 +22,22 @@ SPECS = {
         {"name": "Ethane", "m": 1.6069, "sigma_Angstrom": 3.5206, "epsilon_over_k": 191.42, "BibTeXKey": "Gross-IECR-2001"},
         {"name": "Propane", "m": 2.0020, "sigma_Angstrom": 3.6184, "epsilon_over_k": 208.11, "BibTeXKey": "Gross-IECR-2001"}],
         "kmat": [[0, 0.01, 0.02], [0.01, 0, 0.03], [0.02, 0.03, 0]], "ab": "Liang-IECR-2014"}}, (200, 450), (1, 14000), [0.4, 0.3, 0.3]),
+    "MIE1": ({"kind": "SAFT-VR-Mie", "model": {"names": ["Methane"]}}, (150, 450), (1, 20000), [1.0]),
+    "MIE3": ({"kind": "SAFT-VR-Mie", "model": {"names": ["Methane", "Ethane", "Propane"], "kmat": [[0, 0.01, 0.02], [0.01, 0, 0.03], [0.02, 0.03, 0]]}},
+             (200, 500), (1, 14000), [0.4, 0.3, 0.3]),
+    "GSAFT_WATER": ({"kind": "genericSAFT", "model": {
+        "nonpolar": {"kind": "SAFT-VR-Mie", "model": {"coeffs": [WORKLOADS["C4"]["spec"]["model"]["nonpolar"]["model"]["coeffs"][2]]}},
+        "association": {"kind": "Dufal", "model": {"sigma / m": [3.0555e-10], "epsilon / J/mol": [3475.445374388054], "lambda_r": [35.823],
+                                                   "epsilon_HB / J/mol": [13303.140189045183], "K_HB / m^3": [496.66e-30], "kmat": [[0.0]],
+                                                   "Delta_rule": "Dufal", "molecule_sites": [["e", "e", "H", "H"]]}}}},
+                    (290, 600), (10, 50000), [1.0]),
+    "GSAFT_C4": (WORKLOADS["C4"]["spec"], WORKLOADS["C4"]["T"], WORKLOADS["C4"]["rho"], WORKLOADS["C4"]["z0"]),
+    "GSAFT_CR1": ({"kind": "genericSAFT", "model": {
+        "nonpolar": {"kind": "SAFT-VR-Mie", "model": {"names": ["Methane", "Ethane"]}},
+        "association": {"kind": "canonical", "model": {"b / m^3/mol": [3.1e-5, 4.9e-5], "beta": [0.03, 0.008], "epsilon / J/mol": [12000.0, 18000.0],
+                                                       "Delta_rule": "CR1", "molecule_sites": [["B", "P"], ["N", "N", "P"]],
+                                                       "options": {"alpha": 0.4}}}}},
+                  (250, 500), (10, 15000), [0.55, 0.45]),
     "GERG10": (WORKLOADS["C3"]["spec"], WORKLOADS["C3"]["T"], WORKLOADS["C3"]["rho"], WORKLOADS["C3"]["z0"]),
     "GERG21": (WORKLOADS["C5"]["spec"], WORKLOADS["C5"]["T"], WORKLOADS["C5"]["rho"], WORKLOADS["C5"]["z0"]),
     "GERG2004_3": ({"kind": "GERG2004resid", "model": {"names": ["nitrogen", "methane", "ethane"]}}, (150, 450), (1, 20000), [0.2, 0.7, 0.1]),

@@ -14,6 +14,7 @@
 #include "../../teqp_b200/csrc/tq_gerg.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_iso.cuh"
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
+#include "../../teqp_b200/csrc/tq_assoc.cuh"
 
 using namespace tq;
 
@@ -123,6 +124,10 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             const PcsaftParams& p = *static_cast<const PcsaftParams*>(blob);
             generic_table<PcsaftDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
+        } else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
+            const GsaftParams& p = *static_cast<const GsaftParams*>(blob);
+            generic_table<GsaftDev>(p, p.mie.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
         }
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -138,6 +143,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_atrhoxi<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -154,6 +160,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         IsochoricOut o; o.Psir = f; o.grad = g; o.hess = H; o.lnphi = lnphi; o.phi = phi;
         if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam.rfind("GERG", 0) == 0) gerg_iso_loop(*static_cast<const GergProgram*>(blob), m->R(nullptr, 0), npts, T, rhovec, o);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;

@@ -4,7 +4,8 @@ import pytest
 
 import parity_suite as ps
 
-AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2"]
+AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2",
+            "MIE1", "MIE3", "GSAFT_WATER", "GSAFT_C4", "GSAFT_CR1"]
 
 
 @pytest.mark.parametrize("name", AR_CASES)
@@ -12,12 +13,12 @@ def test_ar_tables(emul, oracle, name):
     ps.ar_tables(ps.EmulBackend(emul), oracle, name, n=1500)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_atrhoxi(emul, oracle, name):
     ps.atrhoxi(ps.EmulBackend(emul), oracle, name, n=200)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isochoric(emul, oracle, name):
     ps.isochoric(ps.EmulBackend(emul), oracle, name, n=300)
 

@@ -12,7 +12,8 @@ import parity_suite as ps
 
 pytestmark = pytest.mark.gpu
 
-AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2"]
+AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2",
+            "MIE1", "MIE3", "GSAFT_WATER", "GSAFT_C4", "GSAFT_CR1"]
 
 
 @pytest.fixture(scope="module")
@@ -27,12 +28,12 @@ def test_ar_tables(be, oracle, name):
     ps.ar_tables(be, oracle, name, n=3000)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_atrhoxi(be, oracle, name):
     ps.atrhoxi(be, oracle, name, n=400)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isochoric(be, oracle, name):
     ps.isochoric(be, oracle, name, n=600)
 
