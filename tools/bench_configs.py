@@ -144,6 +144,36 @@ def main():
                 cb["cores"] = nt
         emit("C2", "PC-SAFT CH4+C2H6: Ar00,01,02,10,11,20 + ln phi", n, ms, nl, 32 + 64, cb)
         del T, rho, x, rv, out
+    # ---- C4: SAFT-VR-Mie ternary + Dufal association on water: the whole get_ATrhoXi table (36 entries x 3 components, of which
+    # the reference exposes 23 x 3) in one launch
+    if want("C4"):
+        w = WORKLOADS["C4"]
+        m = teqp_b200.make_model(w["spec"])
+        n = int(1e7 * args.scale)
+        T, rho, x = synth(w, n)
+        out = torch.empty((3, 3, 3, 4, n), dtype=torch.float64, device=dev)
+        ms, nl = timed(lambda: m.get_ATrhoXi_table_batch(T, rho, x, out=out))
+        cb = None
+        if not args.no_cpu:
+            rm, nt = refmodel(w["spec"])
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from parity_suite import COMBOS_ATRHOXI
+
+            def ref(k):
+                Tn, rn, xn = workload_points("C4", k)
+                for i in range(3):
+                    for (a, b, c) in COMBOS_ATRHOXI:
+                        rm.ATrhoXi(a, b, i, c, Tn, rn, xn)
+            cb = cpu(ref, 32 * nt, seconds=10.0)
+            if cb:
+                cb["cores"] = nt
+        emit("C4", "SAFT-VR-Mie CH4+C2H6+H2O with Dufal association: get_ATrhoXi table (23 combos x 3 comps; 36 x 3 written)", n, ms, nl, 40 + 8 * 108, cb)
+        del T, rho, x, out
+        T, rho, x = synth(w, n)
+        out = torch.empty((5, n), dtype=torch.float64, device=dev)
+        ms, nl = timed(lambda: m.get_Ar0n_batch(4, T, rho, x, out=out))
+        emit("C4-Ar04n", "same model: get_Ar04n", n, ms, nl, 40 + 40, None)
+        del T, rho, x, out
     # ---- C5: GERG-2008 21 components: Psir, gradient, Hessian (441) and ln phi
     if want("C5"):
         w = WORKLOADS["C5"]
