@@ -40,11 +40,13 @@ __global__ void __launch_bounds__(kBlock) gerg_ar_table_kernel(const __grid_cons
                                                                double* __restrict__ out) {
     extern __shared__ double Wsh[];  // [nw][kBlock]; each thread touches only its own column -> no barriers needed
     double* W = Wsh + threadIdx.x;
-    const Exp2K K = Exp2K::load(in.npts >> 62);  // npts < 2^62: the shift is 0, but only at run time
+    Exp2K K = Exp2K::load(in.npts >> 62);  // npts < 2^62: the shift is 0, but only at run time
     const long long npts = in.npts;
     const long long stride = (long long)gridDim.x * kBlock;
     for (long long k = (long long)blockIdx.x * kBlock + threadIdx.x; k < npts; k += stride) {
         const double T = __ldg(in.T + k);
+        // the sign bit of T is 0 for every valid temperature, and thread-dependent
+        K.load_thread((long long)(((unsigned)__double2hiint(T) >> 31) << 3));
         const double rho = __ldg(in.rho + k);
         for (int i = 0; i < P.nc; ++i) W[i * kBlock] = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
         double A[NT + 1][ND + 1];
@@ -201,9 +203,10 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         G.kind = std::get<0>(key); G.l = std::get<1>(key); G.d = std::get<7>(key);
         G.c = std::get<2>(key); G.eta = std::get<3>(key); G.eps = std::get<4>(key); G.beta = std::get<5>(key); G.gamma = std::get<6>(key);
         G.new_h = 1;
+        G.dstep = G.d;
         if (g > 0) {
             const GergGroup& Q = P.group[g - 1];
-            if (Q.kind == G.kind && Q.l == G.l && Q.c == G.c && Q.eta == G.eta && Q.eps == G.eps && Q.beta == G.beta && Q.gamma == G.gamma && Q.d <= G.d) G.new_h = 0;
+            if (Q.kind == G.kind && Q.l == G.l && Q.c == G.c && Q.eta == G.eta && Q.eps == G.eps && Q.beta == G.beta && Q.gamma == G.gamma && Q.d <= G.d) { G.new_h = 0; G.dstep = G.d - Q.d; }
         }
         for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
         G.ntq = (int)bytau.size();

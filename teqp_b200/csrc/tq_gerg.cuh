@@ -44,7 +44,8 @@ struct GergGroup {
     int d, l;        // integer exponents
     int ntq;         // number of distinct tau exponents in this group
     int new_h;       // 1: the exponent h(delta) differs from the previous group's -> recompute the Taylor coefficients of exp(h)
-    int pad_[3];
+    int dstep;       // multiplications by delta that take the running delta^d from the previous group's d (0 after new_h) to this d
+    int pad_[2];
     double c, eta, eps, beta, gamma;
     double bd[kGergND];  // binom(d, m), m = 1..6
     double bl[kGergND];  // binom(l, m), m = 1..6
@@ -130,8 +131,7 @@ TQ_HD void gerg_point(const GergProgram& P, const Exp2K& K, const double T, cons
 
     int rec = 0;
     double E[ND + 1];   // delta^m/m! d^m/ddelta^m exp(h(delta)), shared by consecutive groups with the same h
-    double dd = 1.0;    // running delta^dcur
-    int dcur = 0;
+    double dd = 1.0;    // running delta^d
     for (int g = 0; g < P.ngroup; ++g) {
         const GergGroup& gr = P.group[g];
         if (gr.new_h) {
@@ -161,9 +161,9 @@ TQ_HD void gerg_point(const GergProgram& P, const Exp2K& K, const double T, cons
                 E[m] = s * (1.0 / double(m));
             }
             dd = 1.0;
-            dcur = 0;
         }
-        for (; dcur < gr.d; ++dcur) dd *= delta;
+#pragma unroll 1
+        for (int s = 0; s < gr.dstep; ++s) dd *= delta;
         // G[m] = delta^m/m! d^m/ddelta^m [ delta^d exp(h(delta)) ] = delta^d sum_j binom(d,j) E[m-j]
         double G[ND + 1];
 #pragma unroll
@@ -182,7 +182,7 @@ TQ_HD void gerg_point(const GergProgram& P, const Exp2K& K, const double T, cons
             const double n0 = P.rec[rec + 1].val;
             rec += 2;
             const double t = hd.val;
-            const double e = fast_exp2_bounded(t * l2tau, K);
+            const double e = fast_exp2_prod(t, l2tau, K);
             double c = wload(W, hd.b) * n0;
 #pragma unroll 1
             for (int k = 0; k < hd.a; ++k) {

@@ -11,9 +11,10 @@ __global__ void __launch_bounds__(WS) gerg_isochoric_kernel(const __grid_constan
                                                             const IsochoricOut o) {
     extern __shared__ double Wsh[];  // [rows][WS]; a thread touches only its own column -> no barriers
     double* W = Wsh + threadIdx.x;
-    const Exp2K K = Exp2K::load(in.npts >> 62);
     const long long k = (long long)blockIdx.x * WS + threadIdx.x;
     if (k >= in.npts) return;
+    Exp2K K = Exp2K::load(in.npts >> 62);
+    K.load_thread((long long)(((unsigned)__double2hiint(__ldg(in.T + k)) >> 31) << 3));
     for (int i = 0; i < P.nc; ++i) W[i * WS] = __ldg(in.x + (long long)i * in.x_stride + k);
     gerg_iso_point<WS, WANT_H>(P, K, Rgas, __ldg(in.T + k), W, o, k, in.npts);
 }

@@ -132,7 +132,6 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         int rec = 0;
         double E[NO + 1];
         double dd = 1.0;
-        int dcur = 0;
         for (int g = 0; g < P.ngroup; ++g) {
             const GergGroup& gr = P.group[g];
             if (gr.new_h) {
@@ -160,9 +159,9 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                     E[m] = s * (1.0 / double(m));
                 }
                 dd = 1.0;
-                dcur = 0;
             }
-            for (; dcur < gr.d; ++dcur) dd *= delta;
+#pragma unroll 1
+            for (int s = 0; s < gr.dstep; ++s) dd *= delta;
             double G[NO + 1];
 #pragma unroll
             for (int m = 0; m <= NO; ++m) {
@@ -179,7 +178,7 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                 const double n0 = P.rec[rec + 1].val;
                 rec += 2;
                 const double t = hd.val;
-                const double e = fast_exp2_bounded(t * l2tau, K);
+                const double e = fast_exp2_prod(t, l2tau, K);
                 const double eG0 = e * G[0], eG1 = e * G[1], teG0 = t * eG0;
                 auto acc = [&](const int off, const double n) {
                     double* p = reinterpret_cast<double*>(reinterpret_cast<char*>(aw) + off);

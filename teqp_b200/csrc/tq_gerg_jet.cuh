@@ -1,0 +1,95 @@
+// GERG-2004 / GERG-2008 residual Helmholtz energy over jet types: the SAME factorised term program the headline kernel
+// interprets (tq_gerg.cuh), evaluated in truncated-Taylor arithmetic in 1/T, rho and one composition direction, so that the
+// generic jet-sweep kernels (tq_generic.cuh) serve the composition-derivative entry points of the GERG families:
+// get_ATrhoXi (derivs.hpp:247-292), and anything else that needs derivatives the analytic kernels do not provide.
+//
+// Reference arithmetic: GERG200XReducing::Y (GERG.hpp:179-205, pairs whose denominator's base value is zero are skipped, :189),
+// pure terms :103-122, departure terms :257-274, GERG2008ResidualModel::alphar :1178-1191.
+//     alphar = sum_g  delta^d_g exp(h_g(delta)) * [ sum_{t in g} tau^t * ( sum_{terms (g,t)} n * W_w(x) ) ]
+// Only products of delta and one exponential per density shape are taken in the (rho, x) jet, tau^t = exp(t ln tau) in the (T, x)
+// jet, and the innermost sums in the composition jet alone.
+#pragma once
+#include "tq_gerg.cuh"
+
+namespace tq {
+
+template<int MAXN, class TT, class RT, class XT>
+TQ_HD prom_t<prom_t<TT, RT>, XT> gerg_alphar_jet(const GergProgram& P, const TT& T, const RT& rho, const XT* x) {
+    using TX = prom_t<TT, XT>;
+    using RX = prom_t<RT, XT>;
+    using F = prom_t<TX, RT>;
+    const int nc = P.nc;
+    // reducing functions
+    XT YT(0.0), YV(0.0);
+    {
+        int pidx = 0;
+        for (int i = 0; i < nc; ++i) {
+            const XT xi2 = x[i] * x[i];
+            YT = YT + xi2 * P.Tc[i];
+            YV = YV + xi2 * P.vc[i];
+            for (int j = i + 1; j < nc; ++j, ++pidx) {
+                const GergRedPair pr = P.pair[pidx];
+                const XT dT = x[i] * pr.beta2T + x[j];
+                const XT dV = x[i] * pr.beta2V + x[j];
+                if (base(dT) == 0.0 || base(dV) == 0.0) continue;
+                const XT num = (x[i] * x[j]) * (x[i] + x[j]);
+                YT = YT + (num / dT) * pr.YT2;
+                YV = YV + (num / dV) * pr.YV2;
+            }
+        }
+    }
+    const TX tau = YT * trecip(T);
+    const RX delta = rho * YV;
+    const TX lntau = tlog(tau);
+    // weights
+    XT W[kGergMaxW];
+    for (int i = 0; i < nc; ++i) W[i] = x[i];
+    for (int q = 0; q < P.ndep; ++q) W[nc + q] = (x[P.dep_i[q]] * x[P.dep_j[q]]) * P.depF[q];
+
+    F A(0.0);
+    RX Eh(1.0), dd(1.0);
+    int rec = 0;
+    for (int g = 0; g < P.ngroup; ++g) {
+        const GergGroup& gr = P.group[g];
+        if (gr.new_h) {
+            if (gr.kind == GG_POLY) {
+                Eh = RX(1.0);
+            } else if (gr.kind == GG_EXP) {
+                Eh = texp(tpowi(delta, gr.l) * (-gr.c));
+            } else {
+                const RX de = delta - gr.eps;
+                Eh = texp((de * de) * (-gr.eta) - (delta - gr.gamma) * gr.beta);
+            }
+            dd = RX(1.0);
+        }
+        for (int s = 0; s < gr.dstep; ++s) dd = dd * delta;
+        const RX G = Eh * dd;
+        TX C(0.0);
+        for (int q = 0; q < gr.ntq; ++q) {
+            const GergRec hd = P.rec[rec];
+            const double n0 = P.rec[rec + 1].val;
+            rec += 2;
+            XT c = W[hd.b / (kGergWS * 8)] * n0;
+            for (int k = 0; k < 2 * hd.a; ++k, ++rec) {
+                const GergRec r = P.rec[rec];
+                c = c + W[r.a / (kGergWS * 8)] * r.val;  // padding records carry n = 0
+            }
+            C = C + texp(lntau * hd.val) * c;
+        }
+        A = A + C * G;
+    }
+    return A;
+}
+
+struct GergJetDev {
+    using Params = GergProgram;
+    static constexpr int kMaxC = kGergMaxC;
+    static constexpr bool kNoSmallVariants = true;
+    template<int MAXN, class TT, class RT, class XT>
+    static TQ_HD prom_t<prom_t<TT, RT>, XT> alphar(const Params& p, const TT& T, const RT& rho, const XT* x) {
+        return gerg_alphar_jet<MAXN>(p, T, rho, x);
+    }
+    template<class XT> static TQ_HD double R(const Params& p, const XT*) { return p.Rgas; }
+};
+
+}  // namespace tq

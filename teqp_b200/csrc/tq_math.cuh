@@ -81,30 +81,57 @@ TQ_HD double fast_exp(double x) {
 // operands stay resident in (uniform) registers instead of being re-loaded from constant memory before every use.
 struct Exp2K {
     double c[11];
+    double magic;  // 1.5 * 2^52 in a REGISTER: as an immediate it cannot share a DFMA with a constant-bank operand (t), which costs
+                   // two moves per call; c[10] is likewise wanted in a (vector) register so that the Horner chain can start with
+                   // fma(c10, r, c9) without first copying c10 into the accumulator
     // opaque_zero: any run-time value that is 0 but that the compiler cannot prove to be 0.  With a compile-time-known
     // address ptxas re-materialises the constant loads before every use (~6 loads per call); an address it cannot fold
-    // keeps the coefficients in registers for the whole kernel.
+    // keeps the coefficients in registers for the whole kernel.  opaque_zero_thread: the same, but thread-dependent, so that the
+    // two values loaded through it live in vector registers rather than uniform ones.
     TQ_HD static Exp2K load(long long opaque_zero = 0) {
         Exp2K r;
 #if defined(__CUDA_ARCH__)
         const size_t base = __cvta_generic_to_constant(kExpC_dev + 16) + (size_t)opaque_zero;
 #pragma unroll
         for (int i = 0; i < 11; ++i) asm volatile("ld.const.f64 %0, [%1];" : "=d"(r.c[i]) : "l"(base + 8 * i));
+        asm volatile("ld.const.f64 %0, [%1];" : "=d"(r.magic) : "l"(base - 8 * 3));
 #else
         for (int i = 0; i < 11; ++i) r.c[i] = kExpC_host[16 + i];
+        r.magic = kExpC_host[13];
 #endif
         return r;
+    }
+    // re-load c[10] and magic through a THREAD-dependent zero offset (see above): call once per thread
+    TQ_HD void load_thread(long long opaque_zero_thread) {
+#if defined(__CUDA_ARCH__)
+        const size_t tb = __cvta_generic_to_constant(kExpC_dev) + (size_t)opaque_zero_thread;
+        asm volatile("ld.const.f64 %0, [%1];" : "=d"(c[10]) : "l"(tb + 8 * 26));
+        asm volatile("ld.const.f64 %0, [%1];" : "=d"(magic) : "l"(tb + 8 * 13));
+#else
+        (void)opaque_zero_thread;
+#endif
     }
 };
 
 // 2^y for |y| < 1000 (NOT checked: the caller bounds its argument).  r = y - rint(y) is exact, so the whole error is the
 // polynomial's (1.7e-17) plus Horner rounding: <= 1 ulp.  14 FP64 instructions, no branches.
 TQ_HD double fast_exp2_bounded(double y, const Exp2K& K) {
-    const double t = y + 0x1.8p+52;
-    const double r = y - (t - 0x1.8p+52);
-    double p = K.c[10];
+    const double t = y + K.magic;
+    const double r = y - (t - K.magic);
+    double p = fma(K.c[10], r, K.c[9]);
 #pragma unroll
-    for (int k = 9; k >= 0; --k) p = fma(p, r, K.c[k]);
+    for (int k = 8; k >= 0; --k) p = fma(p, r, K.c[k]);
+    p = fma(p, r, 1.0);
+    return bits_add_exponent(p, bits_lo32(t));
+}
+// 2^(a*b): the product is fused into the rounding step (one DFMA for a*b + magic), the reduced argument r = a*b - n is then
+// exact to one rounding of a*b (fma(a, b, -n))
+TQ_HD double fast_exp2_prod(double a, double b, const Exp2K& K) {
+    const double t = fma(a, b, K.magic);
+    const double r = fma(a, b, -(t - K.magic));
+    double p = fma(K.c[10], r, K.c[9]);
+#pragma unroll
+    for (int k = 8; k >= 0; --k) p = fma(p, r, K.c[k]);
     p = fma(p, r, 1.0);
     return bits_add_exponent(p, bits_lo32(t));
 }
