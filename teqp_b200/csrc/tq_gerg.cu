@@ -96,6 +96,7 @@ public:
     double R(const double*, int) const override { return Rgas; }
     const void* params_blob(size_t* n) const override { *n = sizeof(P); return &P; }
 
+    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gerg_launch_ATrhoXi(P, in, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         gerg_launch_isochoric(P, Rgas, in, o, st);
     }
@@ -144,6 +145,7 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         throw InvalidArgument(std::string("Unable to obtain BIP for the pair {") + fluids[a].name + "," + fluids[b].name + "}");
     };
     P.nc = (int)N;
+    P.Rgas = m->Rgas;
     for (size_t i = 0; i < N; ++i) { P.Tc[i] = fluids[idx[i]].Tc_K; P.vc[i] = 1.0 / fluids[idx[i]].rhoc_molm3; }
 
     std::vector<RawTerm> raw;

@@ -64,6 +64,7 @@ struct alignas(16) GergRec {
 
 struct GergProgram {
     int nc, nw, ndep, npair, ngroup, ntq, nterm, nrec;
+    double Rgas;
     double Tc[kGergMaxC], vc[kGergMaxC];
     double depF[kGergMaxDep];
     unsigned char dep_i[kGergMaxDep], dep_j[kGergMaxDep];
@@ -177,27 +178,50 @@ TQ_HD void gerg_point(const GergProgram& P, const Exp2K& K, const double T, cons
         double C[NT + 1];
 #pragma unroll
         for (int n = 0; n <= NT; ++n) C[n] = 0.0;
-        for (int q = 0; q < gr.ntq; ++q) {
-            const GergRec hd = P.rec[rec];
-            const double n0 = P.rec[rec + 1].val;
-            rec += 2;
-            const double t = hd.val;
-            const double e = fast_exp2_prod(t, l2tau, K);
+        // (g,t) sums two at a time: the two 2^(t log2 tau) Horner chains are independent and interleave, which hides the DFMA
+        // latency that a single 11-deep chain exposes (r01g: "wait" + "short scoreboard" stalls of 5 cycles per issue)
+        auto term_sum = [&](int r, const GergRec& hd, const double n0) {
             double c = wload(W, hd.b) * n0;
 #pragma unroll 1
             for (int k = 0; k < hd.a; ++k) {
-                const GergRec r0 = P.rec[rec], r1 = P.rec[rec + 1];
-                rec += 2;
+                const GergRec r0 = P.rec[r], r1 = P.rec[r + 1];
+                r += 2;
                 c = fma(wload(W, r0.a), r0.val, c);
                 c = fma(wload(W, r1.a), r1.val, c);
             }
-            double v = c * e;
+            return c;
+        };
+        auto accumulate = [&](const double t, double v) {
             C[0] += v;
 #pragma unroll
             for (int n = 1; n <= NT; ++n) {
                 v *= (t - double(n - 1)) * (1.0 / double(n));
                 C[n] += v;
             }
+        };
+        int q = 0;
+#pragma unroll 1
+        for (; q + 1 < gr.ntq; q += 2) {
+            const GergRec hA = P.rec[rec];
+            const double nA = P.rec[rec + 1].val;
+            const int recB = rec + 2 + 2 * hA.a;
+            const GergRec hB = P.rec[recB];
+            const double nB = P.rec[recB + 1].val;
+            const double eA = fast_exp2_prod(hA.val, l2tau, K);
+            const double eB = fast_exp2_prod(hB.val, l2tau, K);
+            const double cA = term_sum(rec + 2, hA, nA);
+            const double cB = term_sum(recB + 2, hB, nB);
+            rec = recB + 2 + 2 * hB.a;
+            accumulate(hA.val, cA * eA);
+            accumulate(hB.val, cB * eB);
+        }
+        if (q < gr.ntq) {
+            const GergRec hd = P.rec[rec];
+            const double n0 = P.rec[rec + 1].val;
+            const double e = fast_exp2_prod(hd.val, l2tau, K);
+            const double c = term_sum(rec + 2, hd, n0);
+            rec += 2 + 2 * hd.a;
+            accumulate(hd.val, c * e);
         }
 #pragma unroll
         for (int n = 0; n <= NT; ++n)

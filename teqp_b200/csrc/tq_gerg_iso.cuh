@@ -312,6 +312,8 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
     }
 }
 
+// host launcher of the jet-sweep get_ATrhoXi table for the GERG families (tq_gerg_jet.cu)
+void gerg_launch_ATrhoXi(const GergProgram& P, const DeviceBatch& in, double* out, cudaStream_t st);
 // host launcher (tq_gerg_iso.cu)
 void gerg_launch_isochoric(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st);
 

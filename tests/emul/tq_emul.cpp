@@ -13,6 +13,7 @@
 #include "../../teqp_b200/csrc/tq_generic.cuh"
 #include "../../teqp_b200/csrc/tq_gerg.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_iso.cuh"
+#include "../../teqp_b200/csrc/tq_gerg_jet.cuh"
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
 #include "../../teqp_b200/csrc/tq_assoc.cuh"
 
@@ -143,6 +144,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam.rfind("GERG", 0) == 0) generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_atrhoxi<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
