@@ -69,6 +69,15 @@ int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, co
 int get_ATrhoXi_table_batch(const long long int uuid, const long long int npts, const double* T, const double* rho,
                             const double* molefrac, const int Ncomp, double* out, const int flags,
                             char* errmsg, int errmsg_length);
+/* cross-composition derivatives of one component pair (i, j) in one sweep (derivs.hpp:294-314, 423-442; replaces the per-combination
+   calls of teqpc.h:8): out[((NT*2+ND)*3+NXi)*3+NXj][k], NT, ND in 0..1, NXi, NXj in 0..2 (x_i and x_j independent) */
+int get_ATrhoXiXj_table_batch(const long long int uuid, const int i, const int j, const long long int npts, const double* T,
+                              const double* rho, const double* molefrac, const int Ncomp, double* out, const int flags,
+                              char* errmsg, int errmsg_length);
+/* ... and of one component triple (derivs.hpp:316-339, 444-465; teqpc.h:9): out[(((NT*2+ND)*2+NXi)*2+NXj)*2+NXk][k], all orders 0..1 */
+int get_ATrhoXiXjXk_table_batch(const long long int uuid, const int i, const int j, const int k, const long long int npts,
+                                const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out,
+                                const int flags, char* errmsg, int errmsg_length);
 /* IsochoricDerivatives::build_Psir_fgradHessian_autodiff (derivs.hpp:1051-1069): f[k], g[i][k], H[i*Ncomp+j][k]; any of f,g,H may be NULL */
 int build_Psir_fgradHessian_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                   const int Ncomp, double* f, double* g, double* H, const int flags,

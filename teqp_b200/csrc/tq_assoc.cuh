@@ -156,6 +156,7 @@ struct GsaftParams {
 struct GsaftDev {
     using Params = GsaftParams;
     static constexpr int kMaxC = kMieMaxC;
+    static constexpr int kCrossOrder = 1;  // order of x_i and x_j in the get_ATrhoXiXj jet (2: full table; 1: mixed entries only)
     static constexpr bool kNoSmallVariants = true;
     template<int MAXN, class TT, class RT, class XT>
     static TQ_HD prom_t<prom_t<TT, RT>, XT> alphar(const Params& p, const TT& T, const RT& rho, const XT* x) {

@@ -276,10 +276,45 @@ int get_ATrhoXi(const long long int uuid, const double T, const int NT, const do
         throw NotImplementedError(name " is not implemented in libteqpb200 yet");                                    \
     })
 
-int get_ATrhoXiXj(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
-                  const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_ATrhoXiXj"); }
-int get_ATrhoXiXjXk(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
-                    const int, const int, const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_ATrhoXiXjXk"); }
+int get_ATrhoXiXj(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND, const double* molefrac,
+                  const int Ncomp, const int i, const int NXi, const int j, const int NXj, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j) throw std::invalid_argument("i cannot equal j");  // derivs.hpp:425-427
+        // combinations the reference compiles (derivs.hpp:294-309): NT+ND <= 1, (NXi, NXj) in {(1,0),(2,0),(0,1),(0,2),(1,1)}
+        const bool ok = NT >= 0 && ND >= 0 && NT + ND <= 1 && NXi >= 0 && NXj >= 0 && NXi + NXj >= 1 && NXi + NXj <= 2;
+        if (!ok) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp) throw std::invalid_argument("component index out of range");
+        double table[36];
+        run(0, 1, {{&T, 1, false}, {&rhomolar, 1, false}, {molefrac, Ncomp, false}}, {{table, 36}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXiXj_table(make_batch(n, din[0], din[1], din[2], false), i, j, dout[0], st);
+                ++g_launches;
+            });
+        *val = table[((NT * 2 + ND) * 3 + NXi) * 3 + NXj];
+    });
+}
+int get_ATrhoXiXjXk(const long long int uuid, const double T, const int NT, const double rhomolar, const int ND, const double* molefrac,
+                    const int Ncomp, const int i, const int NXi, const int j, const int NXj, const int k, const int NXk, double* val,
+                    char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j || j == k || i == k) throw std::invalid_argument("i, j, and k must all be unique");  // derivs.hpp:449-451
+        // derivs.hpp:318-330: NT+ND <= 1, each composition order 0 or 1, at least two of them 1
+        const bool ok = NT >= 0 && ND >= 0 && NT + ND <= 1 && NXi >= 0 && NXi <= 1 && NXj >= 0 && NXj <= 1 && NXk >= 0 && NXk <= 1 && NXi + NXj + NXk >= 2;
+        if (!ok) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp || k < 0 || k >= Ncomp) throw std::invalid_argument("component index out of range");
+        double table[32];
+        run(0, 1, {{&T, 1, false}, {&rhomolar, 1, false}, {molefrac, Ncomp, false}}, {{table, 32}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXiXjXk_table(make_batch(n, din[0], din[1], din[2], false), i, j, k, dout[0], st);
+                ++g_launches;
+            });
+        *val = table[(((NT * 2 + ND) * 2 + NXi) * 2 + NXj) * 2 + NXk];
+    });
+}
 int get_AtaudeltaXi(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
                     const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXi"); }
 int get_AtaudeltaXiXj(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
@@ -344,6 +379,38 @@ int get_ATrhoXi_table_batch(const long long int uuid, const long long int npts, 
         run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, Ncomp * 36}},
             [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
                 m->launch_ATrhoXi_table(make_batch(n, din[0], din[1], din[2], bc), dout[0], st);
+                ++g_launches;
+            });
+    });
+}
+
+int get_ATrhoXiXj_table_batch(const long long int uuid, const int i, const int j, const long long int npts, const double* T, const double* rho,
+                              const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j) throw InvalidArgument("i cannot equal j");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp) throw InvalidArgument("component index out of range");
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, 36}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXiXj_table(make_batch(n, din[0], din[1], din[2], bc), i, j, dout[0], st);
+                ++g_launches;
+            });
+    });
+}
+int get_ATrhoXiXjXk_table_batch(const long long int uuid, const int i, const int j, const int k, const long long int npts, const double* T,
+                                const double* rho, const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg,
+                                int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j || j == k || i == k) throw InvalidArgument("i, j, and k must all be unique");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp || k < 0 || k >= Ncomp) throw InvalidArgument("component index out of range");
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, 32}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_ATrhoXiXjXk_table(make_batch(n, din[0], din[1], din[2], bc), i, j, k, dout[0], st);
                 ++g_launches;
             });
     });

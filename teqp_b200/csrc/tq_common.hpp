@@ -75,6 +75,13 @@ public:
     virtual void launch_ATrhoXi_table(const DeviceBatch&, double*, cudaStream_t) const {
         throw NotImplementedError(std::string("get_ATrhoXi table is not implemented for model family ") + family());
     }
+    // cross-composition tables (derivs.hpp:294-339, 423-465), layouts in tq_generic.cuh
+    virtual void launch_ATrhoXiXj_table(const DeviceBatch&, int, int, double*, cudaStream_t) const {
+        throw NotImplementedError(std::string("get_ATrhoXiXj is not implemented for model family ") + family());
+    }
+    virtual void launch_ATrhoXiXjXk_table(const DeviceBatch&, int, int, int, double*, cudaStream_t) const {
+        throw NotImplementedError(std::string("get_ATrhoXiXjXk is not implemented for model family ") + family());
+    }
     // isochoric family (derivs.hpp:1031-1124, 1208-1230)
     virtual void launch_isochoric(const DeviceBatch&, const IsochoricOut&, cudaStream_t) const {
         throw NotImplementedError(std::string("isochoric derivatives are not implemented for model family ") + family());

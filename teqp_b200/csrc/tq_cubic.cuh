@@ -141,6 +141,7 @@ TQ_HD void cubic_table_point(const CubicParams& p, const double T, const double 
 struct CubicDev {
     using Params = CubicParams;
     static constexpr int kMaxC = kCubicMaxC;
+    static constexpr int kCrossOrder = 2;  // order of x_i and x_j in the get_ATrhoXiXj jet (2: full table; 1: mixed entries only)
     template<int MAXN, class TT, class RT, class XT>
     static TQ_HD prom_t<prom_t<TT, RT>, XT> alphar(const Params& p, const TT& T, const RT& rho, const XT* x) {
         return cubic_alphar<MAXN>(p, T, rho, x);

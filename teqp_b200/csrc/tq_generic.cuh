@@ -190,6 +190,101 @@ void generic_launch_ATrhoXi(const typename M::Params& p, int nc, const DeviceBat
 #endif  // __CUDACC__
 
 // ------------------------------------------------------------------------------------------------------------------
+// Cross-composition derivatives (derivs.hpp:294-339, 423-465): x_i, x_j (, x_k) perturbed independently.
+//   XiXj   table: out[((nt*2+nd)*3+ni)*3+nj][npts], nt, nd in 0..1, ni, nj in 0..2     (the reference exposes 15 of the 36)
+//   XiXjXk table: out[(((nt*2+nd)*2+ni)*2+nj)*2+nk][npts], all orders 0..1              (the reference exposes 12 of the 32)
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN, int NX>
+TQ_HD void generic_ATrhoXiXj_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin,
+                                   const int i, const int j, double* out, const long long ostride) {
+    using XT = J5<0, 0, NX, NX, 0>;
+    using TT = J5<1, 0, 0, 0, 0>;
+    using RT = J5<0, 1, 0, 0, 0>;
+    const TT T = TT::reciprocal_scaled_variable(T0);
+    RT rho;
+    rho.c[0] = Tay<1, Tay<0, Tay<0, Tay<0, double>>>>::scaled_variable(rho0);
+    XT x[MAXN];
+    for (int k = 0; k < nc; ++k) {
+        x[k] = XT(xin[k]);
+        if (k == i) x[k].c[0].c[0].c[1].c[0].c[0] = 1.0;
+        if (k == j) x[k].c[0].c[0].c[0].c[1].c[0] = 1.0;
+    }
+    const J5<1, 1, NX, NX, 0> a = embed<J5<1, 1, NX, NX, 0>>(M::template alphar<MAXN>(p, T, rho, x));
+#pragma unroll
+    for (int nt = 0; nt <= 1; ++nt)
+#pragma unroll
+        for (int nd = 0; nd <= 1; ++nd)
+#pragma unroll
+            for (int ni = 0; ni <= NX; ++ni)
+#pragma unroll
+                for (int nj = 0; nj <= NX; ++nj) {
+                    const double f = (ni == 2 ? 2.0 : 1.0) * (nj == 2 ? 2.0 : 1.0);
+                    out[(long long)(((nt * 2 + nd) * 3 + ni) * 3 + nj) * ostride] = f * a.c[nt].c[nd].c[ni].c[nj].c[0];
+                }
+}
+
+template<class M, int MAXN>
+TQ_HD void generic_ATrhoXiXjXk_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin,
+                                     const int i, const int j, const int kk, double* out, const long long ostride) {
+    using XT = J5<0, 0, 1, 1, 1>;
+    using TT = J5<1, 0, 0, 0, 0>;
+    using RT = J5<0, 1, 0, 0, 0>;
+    const TT T = TT::reciprocal_scaled_variable(T0);
+    RT rho;
+    rho.c[0] = Tay<1, Tay<0, Tay<0, Tay<0, double>>>>::scaled_variable(rho0);
+    XT x[MAXN];
+    for (int k = 0; k < nc; ++k) {
+        x[k] = XT(xin[k]);
+        if (k == i) x[k].c[0].c[0].c[1].c[0].c[0] = 1.0;
+        if (k == j) x[k].c[0].c[0].c[0].c[1].c[0] = 1.0;
+        if (k == kk) x[k].c[0].c[0].c[0].c[0].c[1] = 1.0;
+    }
+    const J5<1, 1, 1, 1, 1> a = embed<J5<1, 1, 1, 1, 1>>(M::template alphar<MAXN>(p, T, rho, x));
+#pragma unroll
+    for (int q = 0; q < 32; ++q)
+        out[(long long)q * ostride] = a.c[(q >> 4) & 1].c[(q >> 3) & 1].c[(q >> 2) & 1].c[(q >> 1) & 1].c[q & 1];
+}
+
+#if defined(__CUDACC__)
+template<class M>
+__global__ void __launch_bounds__(64) generic_ATrhoXiXj_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                               const int i, const int j, double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double x[M::kMaxC];
+        load_x<M, M::kMaxC>(x, nc, in, k);
+        generic_ATrhoXiXj_point<M, M::kMaxC, M::kCrossOrder>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, i, j, out + k, npts);
+    }
+}
+template<class M>
+__global__ void __launch_bounds__(64) generic_ATrhoXiXjXk_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                                 const int i, const int j, const int kk, double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double x[M::kMaxC];
+        load_x<M, M::kMaxC>(x, nc, in, k);
+        generic_ATrhoXiXjXk_point<M, M::kMaxC>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, i, j, kk, out + k, npts);
+    }
+}
+template<class M>
+void generic_launch_ATrhoXiXj(const typename M::Params& p, int nc, const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    generic_ATrhoXiXj_kernel<M><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, i, j, out);
+    TQ_CUDA(cudaGetLastError());
+}
+template<class M>
+void generic_launch_ATrhoXiXjXk(const typename M::Params& p, int nc, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    generic_ATrhoXiXjXk_kernel<M><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, i, j, k, out);
+    TQ_CUDA(cudaGetLastError());
+}
+#endif  // __CUDACC__
+
+// ------------------------------------------------------------------------------------------------------------------
 // Isochoric family.  in.x holds the molar concentrations rhovec[nc][npts]; in.rho is unused.
 // Psi^r(T, rhovec) = alphar(T, sum rhovec, rhovec / sum rhovec) * R(x) * T * sum rhovec      (derivs.hpp:1038-1042)
 // Levels: 1 = unit perturbation of rho_i, 2 = unit perturbation of rho_j.

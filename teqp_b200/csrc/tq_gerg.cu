@@ -12,6 +12,8 @@
 #include "tq_gerg_iso.cuh"
 
 namespace tq {
+void gergjet_launch_ATrhoXiXj(const GergProgram&, const DeviceBatch&, int, int, double*, cudaStream_t);
+void gergjet_launch_ATrhoXiXjXk(const GergProgram&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 
 namespace {
 
@@ -97,6 +99,8 @@ public:
     const void* params_blob(size_t* n) const override { *n = sizeof(P); return &P; }
 
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gerg_launch_ATrhoXi(P, in, out, st); }
+    void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXj(P, in, i, j, out, st); }
+    void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXjXk(P, in, i, j, k, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         gerg_launch_isochoric(P, Rgas, in, o, st);
     }

@@ -84,6 +84,7 @@ TQ_HD prom_t<prom_t<TT, RT>, XT> gerg_alphar_jet(const GergProgram& P, const TT&
 struct GergJetDev {
     using Params = GergProgram;
     static constexpr int kMaxC = kGergMaxC;
+    static constexpr int kCrossOrder = 2;  // order of x_i and x_j in the get_ATrhoXiXj jet (2: full table; 1: mixed entries only)
     static constexpr bool kNoSmallVariants = true;
     template<int MAXN, class TT, class RT, class XT>
     static TQ_HD prom_t<prom_t<TT, RT>, XT> alphar(const Params& p, const TT& T, const RT& rho, const XT* x) {

@@ -308,6 +308,10 @@ template<class T> TQ_HD T tpowi(const T& x, int n) {
 template<int A, int B, int C> using J3 = Tay<A, Tay<B, Tay<C, double>>>;
 template<int A, int B, int C> TQ_HD double coef(const J3<A, B, C>& x, int a, int b, int c) { return x.c[a].c[b].c[c]; }
 
+// Five levels: 1/T, rho and THREE composition directions -- the cross-composition derivatives get_ATrhoXiXj / get_ATrhoXiXjXk
+// (/root/reference/include/teqp/derivs.hpp:294-339, 423-465).  Every jet of one evaluation has this depth.
+template<int A, int B, int C, int D, int E> using J5 = Tay<A, Tay<B, Tay<C, Tay<D, Tay<E, double>>>>>;
+
 TQ_HD double tfact(int k) {
     double f = 1.0;
     for (int i = 2; i <= k; ++i) f *= double(i);

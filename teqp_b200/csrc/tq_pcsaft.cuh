@@ -124,6 +124,7 @@ TQ_HD prom_t<prom_t<TT, RT>, XT> pcsaft_alphar(const PcsaftParams& p, const TT& 
 struct PcsaftDev {
     using Params = PcsaftParams;
     static constexpr int kMaxC = kPcsaftMaxC;
+    static constexpr int kCrossOrder = 1;  // order of x_i and x_j in the get_ATrhoXiXj jet (2: full table; 1: mixed entries only)
     template<int MAXN, class TT, class RT, class XT>
     static TQ_HD prom_t<prom_t<TT, RT>, XT> alphar(const Params& p, const TT& T, const RT& rho, const XT* x) {
         return pcsaft_alphar<MAXN>(p, T, rho, x);

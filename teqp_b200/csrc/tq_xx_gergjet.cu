@@ -1,0 +1,8 @@
+// cross-composition derivative tables (get_ATrhoXiXj, get_ATrhoXiXjXk) for the gergjet family: five-level jet sweeps, see tq_generic.cuh
+#include "tq_common.hpp"
+#include "tq_generic.cuh"
+#include "tq_gerg_jet.cuh"
+namespace tq {
+void gergjet_launch_ATrhoXiXj(const GergProgram& p, const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) { generic_launch_ATrhoXiXj<GergJetDev>(p, p.nc, in, i, j, out, st); }
+void gergjet_launch_ATrhoXiXjXk(const GergProgram& p, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) { generic_launch_ATrhoXiXjXk<GergJetDev>(p, p.nc, in, i, j, k, out, st); }
+}

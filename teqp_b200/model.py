@@ -106,6 +106,28 @@ class Model:
                                              err, C.c_int(2000)), err)
         return ao.obj
 
+    def get_ATrhoXiXj_table_batch(self, i, j, T, rho, x, out=None):
+        """returns [2][2][3][3][npts]: index (NT, ND, NXi, NXj)"""
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((2, 2, 3, 3, n), dev, T, out)
+        ao = _Arg(out, dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_ATrhoXiXj_table_batch(self._uuid, C.c_int(i), C.c_int(j), C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), ao.ptr,
+                                               C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_ATrhoXiXjXk_table_batch(self, i, j, k, T, rho, x, out=None):
+        """returns [2][2][2][2][2][npts]: index (NT, ND, NXi, NXj, NXk)"""
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        out = self._out((2, 2, 2, 2, 2, n), dev, T, out)
+        ao = _Arg(out, dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_ATrhoXiXjXk_table_batch(self._uuid, C.c_int(i), C.c_int(j), C.c_int(k), C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr,
+                                                 C.c_int(nc), ao.ptr, C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
     def _iso(self, fn, T, rhovec, nrows_list):
         dev = _is_torch(T)
         flags = DEVICE_PTRS if dev else 0
@@ -151,6 +173,23 @@ class Model:
         err = C.create_string_buffer(2000)
         _check(lib().get_ATrhoXi(self._uuid, C.c_double(T), C.c_int(NT), C.c_double(rho), C.c_int(ND), z.ctypes.data_as(_dp), C.c_int(z.size),
                                  C.c_int(i), C.c_int(NXi), C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_ATrhoXiXj(self, T, NT, rho, ND, molefrac, i, NXi, j, NXj):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().get_ATrhoXiXj(self._uuid, C.c_double(T), C.c_int(NT), C.c_double(rho), C.c_int(ND), z.ctypes.data_as(_dp), C.c_int(z.size),
+                                   C.c_int(i), C.c_int(NXi), C.c_int(j), C.c_int(NXj), C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_ATrhoXiXjXk(self, T, NT, rho, ND, molefrac, i, NXi, j, NXj, k, NXk):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().get_ATrhoXiXjXk(self._uuid, C.c_double(T), C.c_int(NT), C.c_double(rho), C.c_int(ND), z.ctypes.data_as(_dp), C.c_int(z.size),
+                                     C.c_int(i), C.c_int(NXi), C.c_int(j), C.c_int(NXj), C.c_int(k), C.c_int(NXk), C.byref(out), err,
+                                     C.c_int(2000)), err)
         return out.value
 
     def _one(self, T, rho, molefrac):

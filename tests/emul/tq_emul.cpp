@@ -90,6 +90,16 @@ void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const doub
         else gerg_iso_point<WS, false>(P, K, Rgas, T[k], W.data(), o, k, npts);
     }
 }
+// cross-composition tables: which = 2 -> (i, j) table [36][npts]; which = 3 -> (i, j, k) table [32][npts]
+template<class M>
+void generic_xx(const typename M::Params& p, int nc, int which, int i, int j, int k, long long npts, const double* T, const double* rho, const double* x, double* out) {
+    for (long long q = 0; q < npts; ++q) {
+        double xx[M::kMaxC];
+        for (int c = 0; c < nc; ++c) xx[c] = x[(long long)c * npts + q];
+        if (which == 2) generic_ATrhoXiXj_point<M, M::kMaxC, M::kCrossOrder>(p, nc, T[q], rho[q], xx, i, j, out + q, npts);
+        else generic_ATrhoXiXjXk_point<M, M::kMaxC>(p, nc, T[q], rho[q], xx, i, j, k, out + q, npts);
+    }
+}
 }  // namespace
 
 extern "C" {
@@ -146,6 +156,21 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0) generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_atrhoxi<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else throw InvalidArgument("family not wired in the emulation harness: " + fam);
+        return 0;
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+int emul_cross_table(const char* json, int which, int i, int j, int k, long long npts, const double* T, const double* rho, const double* x,
+                     int ncomp, double* out, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam.rfind("GERG", 0) == 0) generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }

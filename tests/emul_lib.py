@@ -51,6 +51,21 @@ def ATrhoXi_table(spec, T, rho, x):
     return out.reshape(nc, 3, 3, 4, n)
 
 
+def cross_table(spec, idx, T, rho, x):
+    """idx = (i, j) -> [2][2][3][3][n]; idx = (i, j, k) -> [2][2][2][2][2][n]"""
+    T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64); x = np.ascontiguousarray(x, dtype=np.float64)
+    n = T.size; nc = x.shape[0]
+    which = len(idx)
+    out = np.empty((36 if which == 2 else 32, n))
+    err = C.create_string_buffer(1000)
+    i, j = idx[0], idx[1]; k = idx[2] if which == 3 else -1
+    rc = lib().emul_cross_table(json.dumps(spec).encode(), C.c_int(which), C.c_int(i), C.c_int(j), C.c_int(k), C.c_longlong(n), _p(T), _p(rho), _p(x),
+                                C.c_int(nc), _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out.reshape((2, 2, 3, 3, n) if which == 2 else (2, 2, 2, 2, 2, n))
+
+
 def isochoric(spec, T, rhovec, hess=True):
     T = np.ascontiguousarray(T, dtype=np.float64); rv = np.ascontiguousarray(rhovec, dtype=np.float64)
     n = T.size; nc = rv.shape[0]

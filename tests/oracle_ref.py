@@ -106,6 +106,22 @@ class RefModel:
                    C.c_int(x.shape[0]), _p(out))
         return out
 
+    def ATrhoXiXj(self, NT, ND, i, NXi, j, NXj, T, rho, x):
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n)
+        out = np.empty(n)
+        self._call(lib().ref_get_ATrhoXiXj, C.c_int(NT), C.c_int(ND), C.c_int(i), C.c_int(NXi), C.c_int(j), C.c_int(NXj), C.c_longlong(n),
+                   _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
+    def ATrhoXiXjXk(self, NT, ND, i, NXi, j, NXj, k, NXk, T, rho, x):
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n)
+        out = np.empty(n)
+        self._call(lib().ref_get_ATrhoXiXjXk, C.c_int(NT), C.c_int(ND), C.c_int(i), C.c_int(NXi), C.c_int(j), C.c_int(NXj), C.c_int(k), C.c_int(NXk),
+                   C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
     def isochoric_array(self, what, T, rhovec):
         T = np.ascontiguousarray(T, dtype=np.float64)
         n = T.size; rv = _soa(rhovec, n)

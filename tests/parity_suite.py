@@ -25,6 +25,9 @@ class EmulBackend:
     def ATrhoXi_table(self, spec, T, rho, x):
         return self.e.ATrhoXi_table(spec, T, rho, x)
 
+    def cross_table(self, spec, idx, T, rho, x):
+        return self.e.cross_table(spec, idx, T, rho, x)
+
     def isochoric(self, spec, T, rv):
         f, g, H, lnphi, phi = self.e.isochoric(spec, T, rv)
         nc = rv.shape[0]
@@ -57,6 +60,10 @@ class GpuBackend:
 
     def ATrhoXi_table(self, spec, T, rho, x):
         return self.model(spec).get_ATrhoXi_table_batch(T, rho, x)
+
+    def cross_table(self, spec, idx, T, rho, x):
+        m = self.model(spec)
+        return m.get_ATrhoXiXj_table_batch(idx[0], idx[1], T, rho, x) if len(idx) == 2 else m.get_ATrhoXiXjXk_table_batch(idx[0], idx[1], idx[2], T, rho, x)
 
     def isochoric(self, spec, T, rv):
         m = self.model(spec)
@@ -121,6 +128,33 @@ def atrhoxi(be, oracle, name, n=400):
             ref = m.ATrhoXi(NT, ND, i, NX, T, rho, x)
             # third composition derivatives are differences of O(family) terms in both implementations
             parity.check("%s ATrhoXi NT%d ND%d X%d^%d" % (name, NT, ND, i, NX), got[i, NT, ND, NX], ref, fam * (30.0 if NX == 3 else 1.0))
+
+
+COMBOS_XIXJ = [(0, 0, 1, 0), (0, 0, 2, 0), (0, 0, 0, 1), (0, 0, 0, 2), (0, 0, 1, 1), (1, 0, 1, 0), (1, 0, 2, 0), (1, 0, 0, 1), (1, 0, 0, 2), (1, 0, 1, 1),
+               (0, 1, 1, 0), (0, 1, 2, 0), (0, 1, 0, 1), (0, 1, 0, 2), (0, 1, 1, 1)]
+COMBOS_XIXJXK = [(0, 0, 0, 1, 1), (0, 0, 1, 0, 1), (0, 0, 1, 1, 0), (0, 0, 1, 1, 1), (1, 0, 0, 1, 1), (1, 0, 1, 0, 1), (1, 0, 1, 1, 0), (1, 0, 1, 1, 1),
+                 (0, 1, 0, 1, 1), (0, 1, 1, 0, 1), (0, 1, 1, 1, 0), (0, 1, 1, 1, 1)]
+
+
+def cross_composition(be, oracle, name, n=200):
+    """get_ATrhoXiXj (15 combinations, derivs.hpp:294-309) and get_ATrhoXiXjXk (12 combinations, :316-328) for a few index tuples"""
+    spec, T, rho, x = cases.points(name, n)
+    m = oracle.RefModel(spec)
+    nc = x.shape[0]
+    pairs = [(0, 1), (nc - 1, 0)] if nc > 2 else [(0, 1)]
+    for (i, j) in pairs:
+        got = be.cross_table(spec, (i, j), T, rho, x)
+        fam = np.maximum(parity.family_scale(got, (0, 1, 2, 3)), extra_scale(name))
+        for (NT, ND, NXi, NXj) in COMBOS_XIXJ:
+            ref = m.ATrhoXiXj(NT, ND, i, NXi, j, NXj, T, rho, x)
+            parity.check("%s ATrhoXiXj NT%d ND%d x%d^%d x%d^%d" % (name, NT, ND, i, NXi, j, NXj), got[NT, ND, NXi, NXj], ref, fam)
+    if nc >= 3:
+        for (i, j, k) in [(0, 1, 2), (nc - 1, 0, 1)]:
+            got = be.cross_table(spec, (i, j, k), T, rho, x)
+            fam = np.maximum(parity.family_scale(got, (0, 1, 2, 3, 4)), extra_scale(name))
+            for (NT, ND, a, b, c) in COMBOS_XIXJXK:
+                ref = m.ATrhoXiXjXk(NT, ND, i, a, j, b, k, c, T, rho, x)
+                parity.check("%s ATrhoXiXjXk NT%d ND%d %d%d%d" % (name, NT, ND, a, b, c), got[NT, ND, a, b, c], ref, fam)
 
 
 def isochoric(be, oracle, name, n=600, lnphi=True):

@@ -13,7 +13,7 @@ def test_ar_tables(emul, oracle, name):
     ps.ar_tables(ps.EmulBackend(emul), oracle, name, n=1500)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1", "GERG2004_3", "GERG_H2O_CO2", "GERG10"])
 def test_atrhoxi(emul, oracle, name):
     ps.atrhoxi(ps.EmulBackend(emul), oracle, name, n=200)
 
@@ -21,6 +21,11 @@ def test_atrhoxi(emul, oracle, name):
 @pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isochoric(emul, oracle, name):
     ps.isochoric(ps.EmulBackend(emul), oracle, name, n=300)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2"])
+def test_cross_composition(emul, oracle, name):
+    ps.cross_composition(ps.EmulBackend(emul), oracle, name, n=100)
 
 
 def test_gerg_vs_aga8_golden(emul):

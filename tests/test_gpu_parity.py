@@ -28,7 +28,7 @@ def test_ar_tables(be, oracle, name):
     ps.ar_tables(be, oracle, name, n=3000)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "vdW2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1", "GERG2004_3", "GERG_H2O_CO2", "GERG10"])
 def test_atrhoxi(be, oracle, name):
     ps.atrhoxi(be, oracle, name, n=400)
 
@@ -36,6 +36,11 @@ def test_atrhoxi(be, oracle, name):
 @pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isochoric(be, oracle, name):
     ps.isochoric(be, oracle, name, n=600)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2"])
+def test_cross_composition(be, oracle, name):
+    ps.cross_composition(be, oracle, name, n=200)
 
 
 def test_gerg_vs_aga8_golden(be):
