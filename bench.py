@@ -25,6 +25,15 @@ METRIC = "state points/sec (Ar0n n<=4, FP64)"
 UNIT = "points/s"
 
 
+# Only the ONE JSON line may reach stdout: libraries that print to fd 1 (NCCL's version banner, for instance) are diverted to stderr.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -120,7 +129,7 @@ def run_reference(args):
     for s in range(args.warmup + args.steps):
         r = cpu_reference_rate(args.workload, nmax, per_step, "reference templates + AD shim, g++ -O2")
         if r is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libteqp_ref_oracle.so is not built"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref/libteqp_ref_oracle.so is not built"})
             return
         if s >= args.warmup:
             vals.append(r["value"])
@@ -132,7 +141,7 @@ def run_reference(args):
             "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "%s: %s" % (args.workload, json.dumps(w["spec"]["model"].get("names", w["spec"]["kind"])))},
             "cpu_baseline": last, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -259,7 +268,7 @@ def run_ours(args):
             if cb:
                 cb.pop("_check", None)
                 line["cpu_baseline"] = cb
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
