@@ -82,6 +82,15 @@ int get_ATrhoXiXjXk_table_batch(const long long int uuid, const int i, const int
 int build_Psir_fgradHessian_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                   const int Ncomp, double* f, double* g, double* H, const int flags,
                                   char* errmsg, int errmsg_length);
+/* The derived isochoric properties of AbstractModel (teqpcpp.hpp:52-75, 128-160; derivs.hpp:962-978, 1196-1201, 1264-1437, 1482-1494) in one
+   launch; every output may be NULL.  Scalars [k]: get_pr, get_splus, get_dpdT_constrhovec.  Vectors [i][k]: build_d2PsirdTdrhoi_autodiff,
+   get_dpdrhovec_constT, get_partial_molar_volumes, get_chempotVLE_autodiff, get_dchempotdT_autodiff,
+   get_d_ln_fugacity_coefficients_{dT_constrhovec, drho_constTmolefracs, dv_constTmolefracs}.  Matrix [i*Ncomp+j][k]:
+   get_d_ln_fugacity_coefficients_dmolefracs_constTrho (d ln phi_i / d x_j; not symmetric). */
+int isochoric_properties_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const int Ncomp,
+                               double* pr, double* splus, double* dpdT, double* d2PsirdTdrhoi, double* dpdrhovec, double* pmv,
+                               double* chempotVLE, double* dchempotdT, double* dlnphi_dT, double* dlnphi_drho, double* dlnphi_dv,
+                               double* dlnphi_dx, const int flags, char* errmsg, int errmsg_length);
 /* IsochoricDerivatives::get_ln_fugacity_coefficients / get_fugacity_coefficients (derivs.hpp:1208-1230): out[i][k] */
 int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                        const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);

@@ -438,6 +438,32 @@ static void isochoric_call(const Model& m, long long npts, const double* T, cons
         });
 }
 
+int isochoric_properties_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const int Ncomp,
+                               double* pr, double* splus, double* dpdT, double* d2PsirdTdrhoi, double* dpdrhovec, double* pmv,
+                               double* chempotVLE, double* dchempotdT, double* dlnphi_dT, double* dlnphi_drho, double* dlnphi_dv,
+                               double* dlnphi_dx, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (flags & TEQPB200_BROADCAST_X) throw InvalidArgument("TEQPB200_BROADCAST_X does not apply to rhovec inputs");
+        double* ptr[12] = {pr, splus, dpdT, d2PsirdTdrhoi, dpdrhovec, pmv, chempotVLE, dchempotdT, dlnphi_dT, dlnphi_drho, dlnphi_dv, dlnphi_dx};
+        const int rows[12] = {1, 1, 1, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp * Ncomp};
+        std::vector<HostOut> outs;
+        int slot[12];
+        for (int q = 0; q < 12; ++q) { slot[q] = -1; if (ptr[q]) { slot[q] = (int)outs.size(); outs.push_back({ptr[q], rows[q]}); } }
+        if (outs.empty()) return;
+        run(flags, npts, {{T, 1, false}, {rhovec, Ncomp, false}}, outs,
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                IsoPropsOut o;
+                double** f[12] = {&o.pr, &o.splus, &o.dpdT, &o.d2PsirdTdrhoi, &o.dpdrhovec, &o.pmv, &o.chempotVLE, &o.dchempotdT, &o.dlnphi_dT,
+                                  &o.dlnphi_drho, &o.dlnphi_dv, &o.dlnphi_dx};
+                for (int q = 0; q < 12; ++q) if (slot[q] >= 0) *f[q] = dout[slot[q]];
+                m->launch_isoprops(make_batch(n, din[0], nullptr, din[1], false), o, st);
+                ++g_launches;
+            });
+    });
+}
+
 int build_Psir_fgradHessian_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                   const int Ncomp, double* f, double* g, double* H, const int flags, char* errmsg, int errmsg_length) {
     return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, f, g, H, nullptr, nullptr, flags); });

@@ -58,6 +58,22 @@ struct IsochoricOut {
     double* phi = nullptr;         // [ncomp][npts]
 };
 
+// Derived isochoric properties (derivs.hpp:962-978, 1196-1201, 1264-1437, 1482-1494); null pointers are skipped, SoA, row stride npts.
+struct IsoPropsOut {
+    double* pr = nullptr;              // [npts]        get_pr
+    double* splus = nullptr;           // [npts]        get_splus
+    double* dpdT = nullptr;            // [npts]        get_dpdT_constrhovec
+    double* d2PsirdTdrhoi = nullptr;   // [ncomp][npts] build_d2PsirdTdrhoi_autodiff
+    double* dpdrhovec = nullptr;       // [ncomp][npts] get_dpdrhovec_constT
+    double* pmv = nullptr;             // [ncomp][npts] get_partial_molar_volumes
+    double* chempotVLE = nullptr;      // [ncomp][npts] get_chempotVLE_autodiff
+    double* dchempotdT = nullptr;      // [ncomp][npts] get_dchempotdT_autodiff
+    double* dlnphi_dT = nullptr;       // [ncomp][npts] get_d_ln_fugacity_coefficients_dT_constrhovec
+    double* dlnphi_drho = nullptr;     // [ncomp][npts] get_d_ln_fugacity_coefficients_drho_constTmolefracs
+    double* dlnphi_dv = nullptr;       // [ncomp][npts] get_d_ln_fugacity_coefficients_dv_constTmolefracs
+    double* dlnphi_dx = nullptr;       // [ncomp*ncomp][npts] get_d_ln_fugacity_coefficients_dmolefracs_constTrho, (i*ncomp+j) = d ln phi_i / d x_j
+};
+
 class Model {
 public:
     virtual ~Model() = default;
@@ -85,6 +101,9 @@ public:
     // isochoric family (derivs.hpp:1031-1124, 1208-1230)
     virtual void launch_isochoric(const DeviceBatch&, const IsochoricOut&, cudaStream_t) const {
         throw NotImplementedError(std::string("isochoric derivatives are not implemented for model family ") + family());
+    }
+    virtual void launch_isoprops(const DeviceBatch&, const IsoPropsOut&, cudaStream_t) const {
+        throw NotImplementedError(std::string("derived isochoric properties are not implemented for model family ") + family());
     }
     // reducing functions (teqpcpp.hpp get_reducing_density / get_reducing_temperature); host, single composition
     virtual bool reducing(const double*, int, double*, double*) const { return false; }

@@ -17,6 +17,7 @@
 #include "tq_generic.cuh"
 
 namespace tq {
+void cubic_launch_isoprops(const CubicParams&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
 void cubic_launch_ATrhoXiXj(const CubicParams&, const DeviceBatch&, int, int, double*, cudaStream_t);
 void cubic_launch_ATrhoXiXjXk(const CubicParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 
@@ -76,6 +77,7 @@ public:
     }
     void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { cubic_launch_ATrhoXiXj(p, in, i, j, out, st); }
     void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { cubic_launch_ATrhoXiXjXk(p, in, i, j, k, out, st); }
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { cubic_launch_isoprops(p, in, o, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         generic_launch_isochoric<CubicDev>(p, p.nc, in, o, st);
     }

@@ -395,4 +395,117 @@ void generic_launch_isochoric(const typename M::Params& p, int nc, const DeviceB
 
 #endif  // __CUDACC__
 
+// ------------------------------------------------------------------------------------------------------------------
+// Derived isochoric properties (IsoPropsOut): everything the reference composes from Psi^r, its gradient, Hessian-vector
+// products, d/dT of the gradient and a few Lambda_nm (derivs.hpp:962-978, 1196-1201, 1264-1437, 1482-1494).
+// Levels of the jet: 0 = T (UNIT seeded: these are derivatives w.r.t. T itself), 1 = rho_i, 2 = a direction v in rhovec space
+// (v = rhovec gives the Hessian-vector product H rhovec in one sweep per component instead of Nc second-order sweeps).
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN, int A, int B, int C>
+TQ_HD J3<A, B, C> psir_dir_jet(const typename M::Params& p, int nc, double T0, const double* rv, int i, const double* v) {
+    using XT = J3<0, B, C>;
+    XT r[MAXN];
+    XT rhotot(0.0);
+    for (int k = 0; k < nc; ++k) {
+        r[k] = XT(rv[k]);
+        if (B >= 1 && k == i) r[k].c[0].c[B >= 1 ? 1 : 0].c[0] = 1.0;
+        if (C >= 1 && v) r[k].c[0].c[0].c[C >= 1 ? 1 : 0] = v[k];
+        rhotot = rhotot + r[k];
+    }
+    for (int k = 0; k < nc; ++k) r[k] = r[k] / rhotot;
+    using TT = J3<A, 0, 0>;
+    const TT T = TT::unit_variable(T0);
+    const J3<A, B, C> a = embed<J3<A, B, C>>(M::template alphar<MAXN>(p, T, rhotot, r));
+    return (a * M::R(p, r)) * (T * rhotot);
+}
+
+template<class M, int MAXN>
+TQ_HD void generic_isoprops_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const IsoPropsOut& o,
+                                  const long long k, const long long npts) {
+    double rhotot = 0.0;
+    for (int i = 0; i < nc; ++i) rhotot += rv[i];
+    using X0 = J3<0, 0, 0>;
+    X0 x[MAXN];
+    double xd[MAXN];
+    for (int i = 0; i < nc; ++i) { xd[i] = rv[i] / rhotot; x[i] = X0(xd[i]); }
+    const double R = base(M::R(p, x));
+    const double RT = R * T0;
+    // Lambda_nm, n <= 1, m <= 2 at x = rhovec/rhotot
+    double L[2][3];
+    {
+        const J3<1, 0, 0> T = J3<1, 0, 0>::reciprocal_scaled_variable(T0);
+        J3<0, 2, 0> rho;
+        rho.c[0] = Tay<2, Tay<0, double>>::scaled_variable(rhotot);
+        const J3<1, 2, 0> a = embed<J3<1, 2, 0>>(M::template alphar<MAXN>(p, T, rho, x));
+        for (int n = 0; n < 2; ++n)
+            for (int m = 0; m < 3; ++m) L[n][m] = (m == 2 ? 2.0 : 1.0) * a.c[n].c[m].c[0];
+    }
+    const double Z = 1.0 + L[0][1];
+    const double dZdrho = (L[0][1] + L[0][2]) / rhotot;
+    const double dZdT_Z = L[1][1] / (-T0) / Z;
+    if (o.pr) o.pr[k] = L[0][1] * rhotot * R * T0;
+    if (o.splus) o.splus[k] = L[0][0] - L[1][0];
+    double dPsirdT = 0.0, dot_Tgrad = 0.0;
+    const bool want_hx = o.dlnphi_dx != nullptr;
+    for (int i = 0; i < nc; ++i) {
+        const J3<1, 1, 1> d = psir_dir_jet<M, MAXN, 1, 1, 1>(p, nc, T0, rv, i, rv);
+        const double grad = d.c[0].c[1].c[0], Tgrad = d.c[1].c[1].c[0], Hrho = d.c[0].c[1].c[1];
+        dPsirdT = d.c[1].c[0].c[0];
+        dot_Tgrad += rv[i] * Tgrad;
+        const long long q = (long long)i * npts + k;
+        const double dpdrho_i = RT + Hrho;
+        if (o.d2PsirdTdrhoi) o.d2PsirdTdrhoi[q] = Tgrad;
+        if (o.dpdrhovec) o.dpdrhovec[q] = dpdrho_i;
+        if (o.pmv) o.pmv[q] = (-rhotot * dpdrho_i) / (-(rhotot * rhotot) * RT * (1.0 + 2.0 * L[0][1] + L[0][2]));
+        if (o.chempotVLE) o.chempotVLE[q] = grad + RT * (1.0 + log(rv[i]));
+        if (o.dchempotdT) o.dchempotdT[q] = Tgrad + R * (1.0 + log(rv[i]));
+        if (o.dlnphi_dT) o.dlnphi_dT[q] = 1.0 / RT * (Tgrad - 1.0 / T0 * grad) - dZdT_Z;
+        const double dlr = 1.0 / RT * (Hrho / rhotot) - dZdrho / Z;
+        if (o.dlnphi_drho) o.dlnphi_drho[q] = dlr;
+        if (o.dlnphi_dv) o.dlnphi_dv[q] = dlr * (-(rhotot * rhotot));
+    }
+    if (o.dpdT) o.dpdT[k] = rhotot * R - dPsirdT + dot_Tgrad;
+    if (want_hx) {
+        // d ln phi_i / d x_j = rho/(RT) H_ij - (dZ/dx_j)/Z, dZ/dx_j = rho d2alphar/drho dx_j (derivs.hpp:1372-1393)
+        const double f = rhotot / RT;
+        for (int j = 0; j < nc; ++j) {
+            using XT = J3<0, 0, 1>;
+            XT xj[MAXN];
+            for (int c = 0; c < nc; ++c) { xj[c] = XT(xd[c]); if (c == j) xj[c].c[0].c[0].c[1] = 1.0; }
+            J3<0, 1, 0> rho;
+            rho.c[0] = Tay<1, Tay<0, double>>::scaled_variable(rhotot);
+            const J3<0, 1, 1> a = embed<J3<0, 1, 1>>(M::template alphar<MAXN>(p, J3<0, 0, 0>(T0), rho, xj));
+            const double dZdx_Z = a.c[0].c[1].c[1] / Z;
+            // column j of the Hessian: diagonal from a second-order sweep, the rest from mixed first-order sweeps
+            for (int i = 0; i < nc; ++i) {
+                double h;
+                if (i == j) h = 2.0 * psir_jet<M, MAXN, 2, 0>(p, nc, T0, rv, i, -1).c[0].c[2].c[0];
+                else h = psir_jet<M, MAXN, 1, 1>(p, nc, T0, rv, i, j).c[0].c[1].c[1];
+                o.dlnphi_dx[(long long)(i * nc + j) * npts + k] = f * h - dZdx_Z;
+            }
+        }
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M>
+__global__ void __launch_bounds__(64) generic_isoprops_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                              const IsoPropsOut o) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double rv[M::kMaxC];
+        for (int i = 0; i < nc; ++i) rv[i] = __ldg(in.x + (long long)i * in.x_stride + k);
+        generic_isoprops_point<M, M::kMaxC>(p, nc, __ldg(in.T + k), rv, o, k, npts);
+    }
+}
+template<class M>
+void generic_launch_isoprops(const typename M::Params& p, int nc, const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    generic_isoprops_kernel<M><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, o);
+    TQ_CUDA(cudaGetLastError());
+}
+#endif  // __CUDACC__
+
 }  // namespace tq

@@ -12,6 +12,7 @@
 #include "tq_gerg_iso.cuh"
 
 namespace tq {
+void gergjet_launch_isoprops(const GergProgram&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
 void gergjet_launch_ATrhoXiXj(const GergProgram&, const DeviceBatch&, int, int, double*, cudaStream_t);
 void gergjet_launch_ATrhoXiXjXk(const GergProgram&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 
@@ -101,6 +102,7 @@ public:
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gerg_launch_ATrhoXi(P, in, out, st); }
     void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXj(P, in, i, j, out, st); }
     void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXjXk(P, in, i, j, k, out, st); }
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { gergjet_launch_isoprops(P, in, o, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         gerg_launch_isochoric(P, Rgas, in, o, st);
     }

@@ -7,6 +7,7 @@
 #include "tq_pcsaft.cuh"
 
 namespace tq {
+void pcsaft_launch_isoprops(const PcsaftParams&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
 
 // the kernels live in tq_pcsaft_k{1..4}.cu (one translation unit per jet-shape group, compiled in parallel)
 void pcsaft_launch_ar_rho(const PcsaftParams&, int ND, const DeviceBatch&, double*, cudaStream_t);
@@ -60,6 +61,7 @@ public:
         else pcsaft_launch_ar_mixed(p, NT, ND, in, out, st);
     }
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { pcsaft_launch_ATrhoXi(p, in, out, st); }
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { pcsaft_launch_isoprops(p, in, o, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { pcsaft_launch_isochoric(p, in, o, st); }
 };
 

@@ -140,6 +140,25 @@ class Model:
         _check(fn(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *[o.ptr for o in outs], C.c_int(flags), err, C.c_int(2000)), err)
         return [o.obj for o in outs]
 
+    ISOPROPS = ["pr", "splus", "dpdT", "d2PsirdTdrhoi", "dpdrhovec", "pmv", "chempotVLE", "dchempotdT", "dlnphi_dT", "dlnphi_drho", "dlnphi_dv", "dlnphi_dx"]
+
+    def isochoric_properties_batch(self, T, rhovec, which=None):
+        """dict of derived isochoric properties (names: Model.ISOPROPS; teqpcpp.hpp:52-75, 128-160), one launch"""
+        which = list(self.ISOPROPS) if which is None else list(which)
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        nc = rhovec.shape[0]
+        aT, av = _Arg(T, dev), _Arg(rhovec, dev)
+        rows = dict(zip(self.ISOPROPS, [1, 1, 1] + [nc] * 8 + [nc * nc]))
+        outs = {k: _Arg(self._out((rows[k], n), dev, T), dev) for k in which}
+        null = C.POINTER(C.c_double)()
+        ptrs = [outs[k].ptr if k in outs else null for k in self.ISOPROPS]
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().isochoric_properties_batch(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *ptrs, C.c_int(flags), err, C.c_int(2000)), err)
+        return {k: (outs[k].obj[0] if rows[k] == 1 else outs[k].obj) for k in which}
+
     def build_Psir_fgradHessian_batch(self, T, rhovec):
         nc = rhovec.shape[0]
         f, g, H = self._iso(lib().build_Psir_fgradHessian_batch, T, rhovec, [1, nc, nc * nc])

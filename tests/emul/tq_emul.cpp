@@ -100,6 +100,14 @@ void generic_xx(const typename M::Params& p, int nc, int which, int i, int j, in
         else generic_ATrhoXiXjXk_point<M, M::kMaxC>(p, nc, T[q], rho[q], xx, i, j, k, out + q, npts);
     }
 }
+template<class M>
+void generic_ip(const typename M::Params& p, int nc, long long npts, const double* T, const double* rv, const IsoPropsOut& o) {
+    for (long long k = 0; k < npts; ++k) {
+        double r[M::kMaxC];
+        for (int i = 0; i < nc; ++i) r[i] = rv[(long long)i * npts + k];
+        generic_isoprops_point<M, M::kMaxC>(p, nc, T[k], r, o, k, npts);
+    }
+}
 }  // namespace
 
 extern "C" {
@@ -171,6 +179,25 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0) generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else throw InvalidArgument("family not wired in the emulation harness: " + fam);
+        return 0;
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+// outs: the 12 pointers of IsoPropsOut in declaration order (null = skip)
+int emul_isoprops(const char* json, long long npts, const double* T, const double* rhovec, int ncomp, double** outs, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        IsoPropsOut o;
+        o.pr = outs[0]; o.splus = outs[1]; o.dpdT = outs[2]; o.d2PsirdTdrhoi = outs[3]; o.dpdrhovec = outs[4]; o.pmv = outs[5];
+        o.chempotVLE = outs[6]; o.dchempotdT = outs[7]; o.dlnphi_dT = outs[8]; o.dlnphi_drho = outs[9]; o.dlnphi_dv = outs[10]; o.dlnphi_dx = outs[11];
+        if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam.rfind("GERG", 0) == 0) generic_ip<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rhovec, o);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }

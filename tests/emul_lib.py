@@ -66,6 +66,23 @@ def cross_table(spec, idx, T, rho, x):
     return out.reshape((2, 2, 3, 3, n) if which == 2 else (2, 2, 2, 2, 2, n))
 
 
+ISOPROPS = ["pr", "splus", "dpdT", "d2PsirdTdrhoi", "dpdrhovec", "pmv", "chempotVLE", "dchempotdT", "dlnphi_dT", "dlnphi_drho", "dlnphi_dv", "dlnphi_dx"]
+
+
+def isoprops(spec, T, rhovec):
+    """dict of the 12 derived isochoric properties (IsoPropsOut)"""
+    T = np.ascontiguousarray(T, dtype=np.float64); rv = np.ascontiguousarray(rhovec, dtype=np.float64)
+    n = T.size; nc = rv.shape[0]
+    rows = [1, 1, 1] + [nc] * 8 + [nc * nc]
+    outs = [np.empty((r, n)) for r in rows]
+    arr = (C.POINTER(C.c_double) * 12)(*[_p(o) for o in outs])
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_isoprops(json.dumps(spec).encode(), C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), arr, err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return {k: (o[0] if r == 1 else o) for k, o, r in zip(ISOPROPS, outs, rows)}
+
+
 def isochoric(spec, T, rhovec, hess=True):
     T = np.ascontiguousarray(T, dtype=np.float64); rv = np.ascontiguousarray(rhovec, dtype=np.float64)
     n = T.size; nc = rv.shape[0]

@@ -122,6 +122,14 @@ class RefModel:
                    C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
         return out
 
+    def isochoric_scalar(self, what, T, rhovec):
+        """what: 0 get_pr, 1 get_splus, 2 get_dpdT_constrhovec"""
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        n = T.size; rv = _soa(rhovec, n)
+        out = np.empty(n)
+        self._call(lib().ref_isochoric_scalar, C.c_int(what), C.c_longlong(n), _p(T), _p(rv), C.c_int(rv.shape[0]), _p(out))
+        return out
+
     def isochoric_array(self, what, T, rhovec):
         T = np.ascontiguousarray(T, dtype=np.float64)
         n = T.size; rv = _soa(rhovec, n)

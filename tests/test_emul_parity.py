@@ -28,6 +28,11 @@ def test_cross_composition(emul, oracle, name):
     ps.cross_composition(ps.EmulBackend(emul), oracle, name, n=100)
 
 
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10"])
+def test_isoprops(emul, oracle, name):
+    ps.isoprops(ps.EmulBackend(emul), oracle, name, n=100)
+
+
 def test_gerg_vs_aga8_golden(emul):
     ps.gerg_vs_aga8_golden(ps.EmulBackend(emul))
 

@@ -43,6 +43,11 @@ def test_cross_composition(be, oracle, name):
     ps.cross_composition(be, oracle, name, n=200)
 
 
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10"])
+def test_isoprops(be, oracle, name):
+    ps.isoprops(be, oracle, name, n=300)
+
+
 def test_gerg_vs_aga8_golden(be):
     ps.gerg_vs_aga8_golden(be)
 
