@@ -4,7 +4,7 @@ set -u
 mkdir -p gpurun_out
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 tail -5 gpurun_out/pytest_gpu.log
-timeout 900 python tools/bench_configs.py --only C4,C5 > gpurun_out/bench_configs.jsonl 2> gpurun_out/bench_configs.err; echo "bench_configs rc=$?"
+timeout 900 python tools/bench_configs.py --only C5 > gpurun_out/bench_configs.jsonl 2> gpurun_out/bench_configs.err; echo "bench_configs rc=$?"
 cat gpurun_out/bench_configs.jsonl; tail -3 gpurun_out/bench_configs.err
 SHORT="python tools/bench_configs.py --only C5 --no-cpu --scale 0.2 --steps 1 --warmup 1"
 timeout 300 $SHORT > gpurun_out/plain_c5.log 2>&1 &&
