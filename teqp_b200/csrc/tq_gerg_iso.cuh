@@ -79,10 +79,7 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                 const GergRedPair pr = P.pair[pidx];
                 const double dT = fma(pr.beta2T, ri, rj), dV = fma(pr.beta2V, ri, rj);
                 const double den = dT * dV;
-                if (den == 0.0) {  // both concentrations zero: the reference skips the pair (GERG.hpp:189)
-                    if (WANT_H) { o.hess[((long long)nc * i + j) * npts + k] = 0.0; o.hess[((long long)nc * j + i) * npts + k] = 0.0; }
-                    continue;
-                }
+                if (den == 0.0) continue;  // both concentrations zero: the reference skips the pair (GERG.hpp:189)
                 const double inv = fast_rcp(den);
                 const double invT = inv * dV, invV = inv * dT;
                 const GergPairD a = gerg_pair_first(pr.beta2T, ri, rj, invT);
@@ -98,11 +95,6 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                     hVi = fma(pr.YV2, 2.0 * fma(-b.fi, pr.beta2V, rj) * invV, hVi);
                     hT[j * WS] = fma(pr.YT2, 2.0 * (ri - a.fj) * invT, hT[j * WS]);
                     hV[j * WS] = fma(pr.YV2, 2.0 * (ri - b.fj) * invV, hV[j * WS]);
-                    // the pair's mixed second derivatives d2Y_T/drho_i drho_j, d2Y_V/drho_i drho_j are parked in the two Hessian slots
-                    // of the pair (same thread reads them back in pass C): the pair is not evaluated a second time
-                    const double s2 = 2.0 * (ri + rj);
-                    o.hess[((long long)nc * i + j) * npts + k] = pr.YT2 * (fma(-a.fj, pr.beta2T, s2 - a.fi) * invT);
-                    o.hess[((long long)nc * j + i) * npts + k] = pr.YV2 * (fma(-b.fj, pr.beta2V, s2 - b.fi) * invV);
                 }
             }
             vt[i * WS] += gTi;
@@ -279,8 +271,9 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
     // ---- pass C: Hessian ------------------------------------------------------------------------------------------------
     const double const0 = (2.0 * S0r + 2.0 * Fs * invr + Fr * invr) * invr;
     const long long ncl = nc;
-    int qn = 0;
+    int pidx = 0, qn = 0;
     for (int i = 0; i < nc; ++i) {
+        const double ri = W[i * WS];
         const double gTi = vt[i * WS], gVi = vd[i * WS];
         const double ti = gTi - 2.0 * invr, di = gVi - invr;
         const double Pi = Pv[i * WS], Qi = Qv[i * WS], csi = as[i * WS], cri = ar[i * WS], Ei = Ev[i * WS];
@@ -291,32 +284,30 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
             h += 2.0 * Ei + const0;
             o.hess[(ncl * i + i) * npts + k] = RT * h;
         }
-        for (int j0 = i + 1; j0 < nc; j0 += 4) {
-            double mT[4], mV[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int j = j0 + u;
-                if (j < nc) {
-                    mT[u] = o.hess[(ncl * i + j) * npts + k];
-                    mV[u] = o.hess[(ncl * j + i) * npts + k];
-                }
+        for (int j = i + 1; j < nc; ++j, ++pidx) {
+            const double rj = W[j * WS];
+            const GergRedPair pr = P.pair[pidx];
+            const double dT = fma(pr.beta2T, ri, rj), dV = fma(pr.beta2V, ri, rj);
+            const double den = dT * dV;
+            double yT = 0.0, yV = 0.0;  // Y_ij / Y
+            if (den != 0.0) {
+                const double inv = fast_rcp(den);
+                const double invT = inv * dV, invV = inv * dT;
+                const GergPairD a = gerg_pair_first(pr.beta2T, ri, rj, invT);
+                const GergPairD b = gerg_pair_first(pr.beta2V, ri, rj, invV);
+                yT = pr.YT2 * iYT * (fma(-a.fj, pr.beta2T, 2.0 * (ri + rj) - a.fi) * invT);
+                yV = pr.YV2 * iYV * (fma(-b.fj, pr.beta2V, 2.0 * (ri + rj) - b.fi) * invV);
             }
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int j = j0 + u;
-                if (j < nc) {
-                    const double gTj = vt[j * WS], gVj = vd[j * WS];
-                    const double tj = gTj - 2.0 * invr, dj = gVj - invr;
-                    double h = fma(tj, Pi, fma(dj, Qi, fma(ti, as[j * WS], di * ar[j * WS])));
-                    h = fma(Fs, fma(-gTi, gTj, mT[u] * iYT), h);
-                    h = fma(Fr, fma(-gVi, gVj, mV[u] * iYV), h);
-                    h += Ei + Ev[j * WS] + const0;
-                    if (qn < P.ndep && P.dep_i[qn] == i && P.dep_j[qn] == j) { h = fma(aw[(nc + qn) * WS], invr, h); ++qn; }
-                    h *= RT;
-                    o.hess[(ncl * i + j) * npts + k] = h;
-                    o.hess[(ncl * j + i) * npts + k] = h;
-                }
-            }
+            const double gTj = vt[j * WS], gVj = vd[j * WS];
+            const double tj = gTj - 2.0 * invr, dj = gVj - invr;
+            double h = fma(tj, Pi, fma(dj, Qi, fma(ti, as[j * WS], di * ar[j * WS])));
+            h = fma(Fs, fma(-gTi, gTj, yT), h);
+            h = fma(Fr, fma(-gVi, gVj, yV), h);
+            h += Ei + Ev[j * WS] + const0;
+            if (qn < P.ndep && P.dep_i[qn] == i && P.dep_j[qn] == j) { h = fma(aw[(nc + qn) * WS], invr, h); ++qn; }
+            h *= RT;
+            o.hess[(ncl * i + j) * npts + k] = h;
+            o.hess[(ncl * j + i) * npts + k] = h;
         }
     }
 }
