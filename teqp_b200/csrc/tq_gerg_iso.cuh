@@ -28,7 +28,11 @@
 
 namespace tq {
 
-TQ_HD constexpr int gerg_iso_rows(int nc, int nw, bool want_h) { return want_h ? 4 * nw + 7 * nc : 2 * nw + 2 * nc; }
+// rows of the staging area.  Hessian path: weights, three per-weight arrays, the Nc-vectors dlnY_T, dlnY_V and the running diagonal
+// sums; the vector E lives in rows that are free once the departure weights have been reduced (2 ndep of them), plus nc - 2 ndep
+// extra rows for mixtures with few departure functions.
+TQ_HD constexpr int gerg_iso_extra_rows(int nc, int nw) { return nc - 2 * (nw - nc) > 0 ? nc - 2 * (nw - nc) : 0; }
+TQ_HD constexpr int gerg_iso_rows(int nc, int nw, bool want_h) { return want_h ? 4 * nw + 3 * nc + gerg_iso_extra_rows(nc, nw) : 2 * nw + 2 * nc; }
 
 // value, first and (H) second derivatives of one reducing pair term f = ri rj (ri + rj) / (b2 ri + rj); inv = 1/(b2 ri + rj)
 struct GergPairD { double f, fi, fj; };
@@ -52,11 +56,13 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
     double* ar = WANT_H ? as + (size_t)nw * WS : aw;
     double* vt = WANT_H ? ar + (size_t)nw * WS : aw + (size_t)nw * WS;
     double* vd = vt + (size_t)nc * WS;
-    double* hT = vd + (size_t)nc * WS;  // only touched when WANT_H
-    double* hV = hT + (size_t)nc * WS;
-    double* Ev = hV + (size_t)nc * WS;
-    double* Pv = Ev + (size_t)nc * WS;
-    double* Qv = Pv + (size_t)nc * WS;
+    double* hd = vd + (size_t)nc * WS;  // only touched when WANT_H: running sums of the diagonal second derivatives of Y_T, Y_V
+    double* Ex = hd + (size_t)nc * WS;  // extra rows of E (mixtures with fewer than nc/2 departure functions)
+    const int ndep = P.ndep;
+    // E_k: rows of the departure weights (W) and of their a_w,s sums (as) are dead after the reductions; E moves in there
+    auto Eref = [&](const int kk) -> double& {
+        return (kk < ndep) ? W[(nc + kk) * WS] : (kk < 2 * ndep) ? as[(nc + kk - ndep) * WS] : Ex[(kk - 2 * ndep) * WS];
+    };
 
     // ---- pass A: Y_T, Y_V at rhovec, gradients, diagonal second derivatives --------------------------------------------
     double rhotot = 0.0, YT = 0.0, YV = 0.0;
@@ -67,13 +73,12 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         YV = fma(ri * ri, P.vc[i], YV);
         vt[i * WS] = 2.0 * ri * P.Tc[i];
         vd[i * WS] = 2.0 * ri * P.vc[i];
-        if (WANT_H) { hT[i * WS] = 2.0 * P.Tc[i]; hV[i * WS] = 2.0 * P.vc[i]; }
     }
     {
         int pidx = 0;
         for (int i = 0; i < nc; ++i) {
             const double ri = W[i * WS];
-            double gTi = 0.0, gVi = 0.0, hTi = 0.0, hVi = 0.0;
+            double gTi = 0.0, gVi = 0.0;
             for (int j = i + 1; j < nc; ++j, ++pidx) {
                 const double rj = W[j * WS];
                 const GergRedPair pr = P.pair[pidx];
@@ -90,27 +95,19 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                 gVi = fma(pr.YV2, b.fi, gVi);
                 vt[j * WS] = fma(pr.YT2, a.fj, vt[j * WS]);
                 vd[j * WS] = fma(pr.YV2, b.fj, vd[j * WS]);
-                if (WANT_H) {
-                    hTi = fma(pr.YT2, 2.0 * fma(-a.fi, pr.beta2T, rj) * invT, hTi);
-                    hVi = fma(pr.YV2, 2.0 * fma(-b.fi, pr.beta2V, rj) * invV, hVi);
-                    hT[j * WS] = fma(pr.YT2, 2.0 * (ri - a.fj) * invT, hT[j * WS]);
-                    hV[j * WS] = fma(pr.YV2, 2.0 * (ri - b.fj) * invV, hV[j * WS]);
-                }
             }
             vt[i * WS] += gTi;
             vd[i * WS] += gVi;
-            if (WANT_H) { hT[i * WS] += hTi; hV[i * WS] += hVi; }
         }
     }
     const double invr = 1.0 / rhotot;
     const double iYT = 1.0 / YT, iYV = 1.0 / YV;
     const double tau = YT * (invr * invr) / T;
     const double delta = YV * invr;
-    // vt, vd, hT, hV -> dlnY/drho_k and Y_kk/Y (the -2/rho, -1/rho of ln tau, ln delta are added where they are used)
+    // vt, vd -> dlnY/drho_k (the -2/rho, -1/rho of ln tau, ln delta are added where they are used)
     for (int i = 0; i < nc; ++i) {
         vt[i * WS] *= iYT;
         vd[i * WS] *= iYV;
-        if (WANT_H) { hT[i * WS] *= iYT; hV[i * WS] *= iYV; }
     }
     for (int q = 0; q < P.ndep; ++q) W[(nc + q) * WS] = W[P.dep_i[q] * WS] * W[P.dep_j[q] * WS] * P.depF[q] * invr;
     for (int w = 0; w < nw; ++w) {
@@ -221,8 +218,6 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
     const double RT = Rgas * T;
     const double Fs = A[1][0], Fr = A[0][1];
     double S0 = 0.0, Ss = 0.0, Sr = 0.0;
-    if (WANT_H)
-        for (int i = 0; i < nc; ++i) Ev[i * WS] = 0.0;
     for (int q = 0; q < P.ndep; ++q) {
         const int i = P.dep_i[q], j = P.dep_j[q];
         const double wq = W[(nc + q) * WS], ri = W[i * WS], rj = W[j * WS];
@@ -233,8 +228,6 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         aw[i * WS] = fma(m0 * invr, rj, aw[i * WS]);
         aw[j * WS] = fma(m0 * invr, ri, aw[j * WS]);
         if (WANT_H) {
-            Ev[i * WS] = fma(m0, rj, Ev[i * WS]);
-            Ev[j * WS] = fma(m0, ri, Ev[j * WS]);
             const double ms = F * as[(nc + q) * WS] * invr, mr = F * ar[(nc + q) * WS] * invr;
             Ss = fma(as[(nc + q) * WS], wq, Ss);
             Sr = fma(ar[(nc + q) * WS], wq, Sr);
@@ -261,14 +254,22 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
             const double cs = as[i * WS] - Ssr, cr = ar[i * WS] - Srr;
             as[i * WS] = cs;
             ar[i * WS] = cr;
-            Pv[i * WS] = fma(Fss, tk, fma(Fsr, dk, cs));
-            Qv[i * WS] = fma(Fsr, tk, fma(Frr, dk, cr));
-            Ev[i * WS] *= -invr2;
         }
     }
     if (!WANT_H) return;
 
-    // ---- pass C: Hessian ------------------------------------------------------------------------------------------------
+    // ---- E_k = -(1/rho^2) sum_{q contains k} M_q rho_other, into the rows the departure weights no longer need -------------
+    for (int i = 0; i < nc; ++i) Eref(i) = 0.0;
+    for (int q = 0; q < ndep; ++q) {
+        const int i = P.dep_i[q], j = P.dep_j[q];
+        const double m0 = -invr2 * aw[(nc + q) * WS];
+        Eref(i) = fma(m0, W[j * WS], Eref(i));
+        Eref(j) = fma(m0, W[i * WS], Eref(j));
+    }
+    // ---- pass C: Hessian.  Each pair's reducing term is evaluated again here for its three second derivatives; the diagonal
+    // ones are summed as they come (hd[j] collects what rows i < j contribute to H_jj) ---------------------------------------
+    const double FsY = Fs * iYT, FrY = Fr * iYV;  // Phi_s / Y_T, Phi_r / Y_V
+    for (int i = 0; i < nc; ++i) hd[i * WS] = 2.0 * fma(FsY, P.Tc[i], FrY * P.vc[i]);
     const double const0 = (2.0 * S0r + 2.0 * Fs * invr + Fr * invr) * invr;
     const long long ncl = nc;
     int pidx = 0, qn = 0;
@@ -276,14 +277,9 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         const double ri = W[i * WS];
         const double gTi = vt[i * WS], gVi = vd[i * WS];
         const double ti = gTi - 2.0 * invr, di = gVi - invr;
-        const double Pi = Pv[i * WS], Qi = Qv[i * WS], csi = as[i * WS], cri = ar[i * WS], Ei = Ev[i * WS];
-        {
-            double h = fma(ti, Pi, fma(di, Qi, fma(ti, csi, di * cri)));
-            h = fma(Fs, fma(-gTi, gTi, hT[i * WS]), h);
-            h = fma(Fr, fma(-gVi, gVi, hV[i * WS]), h);
-            h += 2.0 * Ei + const0;
-            o.hess[(ncl * i + i) * npts + k] = RT * h;
-        }
+        const double csi = as[i * WS], cri = ar[i * WS], Ei = Eref(i);
+        const double Pi = fma(Fss, ti, fma(Fsr, di, csi)), Qi = fma(Fsr, ti, fma(Frr, di, cri));
+        double hdi = hd[i * WS];
         for (int j = i + 1; j < nc; ++j, ++pidx) {
             const double rj = W[j * WS];
             const GergRedPair pr = P.pair[pidx];
@@ -295,19 +291,30 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
                 const double invT = inv * dV, invV = inv * dT;
                 const GergPairD a = gerg_pair_first(pr.beta2T, ri, rj, invT);
                 const GergPairD b = gerg_pair_first(pr.beta2V, ri, rj, invV);
-                yT = pr.YT2 * iYT * (fma(-a.fj, pr.beta2T, 2.0 * (ri + rj) - a.fi) * invT);
-                yV = pr.YV2 * iYV * (fma(-b.fj, pr.beta2V, 2.0 * (ri + rj) - b.fi) * invV);
+                const double s2 = 2.0 * (ri + rj);
+                const double wT = pr.YT2 * FsY * invT, wV = pr.YV2 * FrY * invV;
+                yT = pr.YT2 * iYT * (fma(-a.fj, pr.beta2T, s2 - a.fi) * invT);
+                yV = pr.YV2 * iYV * (fma(-b.fj, pr.beta2V, s2 - b.fi) * invV);
+                hdi = fma(wT, 2.0 * fma(-a.fi, pr.beta2T, rj), fma(wV, 2.0 * fma(-b.fi, pr.beta2V, rj), hdi));
+                hd[j * WS] = fma(wT, 2.0 * (ri - a.fj), fma(wV, 2.0 * (ri - b.fj), hd[j * WS]));
             }
             const double gTj = vt[j * WS], gVj = vd[j * WS];
             const double tj = gTj - 2.0 * invr, dj = gVj - invr;
             double h = fma(tj, Pi, fma(dj, Qi, fma(ti, as[j * WS], di * ar[j * WS])));
             h = fma(Fs, fma(-gTi, gTj, yT), h);
             h = fma(Fr, fma(-gVi, gVj, yV), h);
-            h += Ei + Ev[j * WS] + const0;
-            if (qn < P.ndep && P.dep_i[qn] == i && P.dep_j[qn] == j) { h = fma(aw[(nc + qn) * WS], invr, h); ++qn; }
+            h += Ei + Eref(j) + const0;
+            if (qn < ndep && P.dep_i[qn] == i && P.dep_j[qn] == j) { h = fma(aw[(nc + qn) * WS], invr, h); ++qn; }
             h *= RT;
             o.hess[(ncl * i + j) * npts + k] = h;
             o.hess[(ncl * j + i) * npts + k] = h;
+        }
+        {
+            double h = fma(ti, Pi, fma(di, Qi, fma(ti, csi, di * cri)));
+            h = fma(-Fs * gTi, gTi, h);
+            h = fma(-Fr * gVi, gVi, h);
+            h += hdi + 2.0 * Ei + const0;
+            o.hess[(ncl * i + i) * npts + k] = RT * h;
         }
     }
 }
