@@ -139,7 +139,9 @@ def run_reference(args):
     last["value"] = v
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": None, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, json.dumps(w["spec"]["model"].get("names", w["spec"]["kind"])))},
+            "config": {"workload": "%s: GERG-2008 residual, %d components, get_Ar0%dn (SURVEY 8d synthetic grid; bounded sample per step, see cpu_baseline.sample)"
+                                   % (args.workload, len(w["spec"]["model"].get("names", [])), nmax),
+                       "components": w["spec"]["model"].get("names", w["spec"]["kind"])},
             "cpu_baseline": last, "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     emit(line)
 
