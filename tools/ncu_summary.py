@@ -8,8 +8,11 @@ raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_outpu
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, vals = rows[0], rows[2]
 d = dict(zip(hdr, vals))
+units = dict(zip(hdr, rows[1]))
 f = lambda k: float(d[k])
-out = {"kernel": d.get("Kernel Name"), "points": npts, "time_ms": f("gpu__time_duration.sum"),
+# ncu picks the unit per report (us for short launches, ms for long ones): normalise to ms
+t_scale = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}.get(units.get("gpu__time_duration.sum", "ms"), 1.0)
+out = {"kernel": d.get("Kernel Name"), "points": npts, "time_ms": f("gpu__time_duration.sum") * t_scale,
        "regs": f("launch__registers_per_thread"), "grid": f("launch__grid_size"), "block": f("launch__block_size"),
        "warps_active_pct": f("sm__warps_active.avg.pct_of_peak_sustained_active"),
        "fp64_pipe_active_pct": f("sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"),
