@@ -114,6 +114,12 @@ int teqpb200_synth_points(const long long int npts, const long long int k0, cons
                           const double Thi, const double rholo, const double rhohi, const double* z0_host, const int Ncomp,
                           double* T, double* rho, double* x, char* errmsg, int errmsg_length);
 
+/* Per-model generated kernels (GERG-2004/2008: csrc/tq_gerg_jit.hpp).  which = 0: the generated CUDA C translation unit for the
+   Lambda^r table of shape (NT, ND), NUL-terminated; which = 1: its constant pool (doubles); which = 2: the sm_100a cubin NVRTC makes of
+   it (no device needed).  Writes min(*nbytes, needed) bytes into buf (buf may be NULL) and returns the needed size in *nbytes. */
+int teqpb200_generated_kernel(const long long int uuid, const int NT, const int ND, const int which, void* buf,
+                              unsigned long long* nbytes, char* errmsg, int errmsg_length);
+
 #ifdef __cplusplus
 }
 #endif

@@ -141,7 +141,7 @@ template<size_t N, typename T, typename U, std::enable_if_t<isArithmetic<U>, int
         const long n = static_cast<long>(e_);
         if (static_cast<T>(n) == e && n >= 0) return powint(a, n);
     }
-    Real<N,T> r; r.c[0] = pow(a.c[0], e);
+    Real<N,T> r; r.c[0] = pow(a.c[0], e_);  // the arithmetic exponent goes down unchanged, so nested Real<N,Real<M,T>> keeps this rule at every level
     for (size_t k = 1; k <= N; ++k) { T s = 0; for (size_t j = 1; j <= k; ++j) s += (e * T(j) - T(k - j)) * a.c[j] * r.c[k - j]; r.c[k] = s / (T(k) * a.c[0]); }
     return r;
 }

@@ -20,11 +20,34 @@ HEAD struct ScalarBinaryOpTraits<AD, double, Op> { typedef AD ReturnType; }; \
 HEAD struct ScalarBinaryOpTraits<double, AD, Op> { typedef AD ReturnType; }; \
 HEAD struct ScalarBinaryOpTraits<AD, int, Op> { typedef AD ReturnType; }; \
 HEAD struct ScalarBinaryOpTraits<int, AD, Op> { typedef AD ReturnType; };
+#define SHIM_BINOP_TRAITS_Q(HEAD, AD) \
+HEAD struct ScalarBinaryOpTraits<AD, __float128, Op> { typedef AD ReturnType; }; \
+HEAD struct ScalarBinaryOpTraits<__float128, AD, Op> { typedef AD ReturnType; };
 #define SHIM_COMMA ,
 SHIM_BINOP_TRAITS(template<typename T SHIM_COMMA typename G SHIM_COMMA typename Op>, autodiff::detail::Dual<T SHIM_COMMA G>)
 SHIM_BINOP_TRAITS(template<size_t N SHIM_COMMA typename T SHIM_COMMA typename Op>, autodiff::detail::Real<N SHIM_COMMA T>)
+#if defined(SHIM_QUAD)
+// __float128 as an Eigen scalar and as the innermost coefficient type of Real / Dual (oracle/ref_truth.cpp only)
+template<> struct NumTraits<__float128> : GenericNumTraits<__float128> {
+    typedef __float128 Real; typedef __float128 NonInteger; typedef __float128 Nested; typedef __float128 Literal;
+    enum { IsComplex = 0, IsInteger = 0, IsSigned = 1, RequireInitialization = 0, ReadCost = 2, AddCost = 8, MulCost = 16 };
+    static inline __float128 epsilon() { return 1.92592994438723585305597794258492732e-34Q; }
+    static inline __float128 dummy_precision() { return 1e-30Q; }
+    static inline __float128 highest() { return 1.18973149535723176508575932662800702e4932Q; }
+    static inline __float128 lowest() { return -1.18973149535723176508575932662800702e4932Q; }
+    static inline int digits10() { return 33; }
+    static inline int digits() { return 113; }
+};
+template<typename Op> struct ScalarBinaryOpTraits<__float128, double, Op> { typedef __float128 ReturnType; };
+template<typename Op> struct ScalarBinaryOpTraits<double, __float128, Op> { typedef __float128 ReturnType; };
+template<typename Op> struct ScalarBinaryOpTraits<__float128, int, Op> { typedef __float128 ReturnType; };
+template<typename Op> struct ScalarBinaryOpTraits<int, __float128, Op> { typedef __float128 ReturnType; };
+SHIM_BINOP_TRAITS_Q(template<typename T SHIM_COMMA typename G SHIM_COMMA typename Op>, autodiff::detail::Dual<T SHIM_COMMA G>)
+SHIM_BINOP_TRAITS_Q(template<size_t N SHIM_COMMA typename T SHIM_COMMA typename Op>, autodiff::detail::Real<N SHIM_COMMA T>)
+#endif
 #undef SHIM_COMMA
 #undef SHIM_BINOP_TRAITS
+#undef SHIM_BINOP_TRAITS_Q
 }
 
 namespace autodiff {

@@ -486,6 +486,23 @@ int teqpb200_get_R(const long long int uuid, const double* molefrac, const int N
 int teqpb200_get_ncomp(const long long int uuid, int* Ncomp, char* errmsg, int errmsg_length) {
     return guarded(false, errmsg, errmsg_length, [&] { *Ncomp = lookup(uuid)->ncomp(); });
 }
+int teqpb200_generated_kernel(const long long int uuid, const int NT, const int ND, const int which, void* buf, unsigned long long* nbytes,
+                              char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        std::vector<char> bytes;
+        if (which == 2) bytes = m->jit_cubin(NT, ND);
+        else {
+            std::vector<double> consts;
+            const std::string src = m->jit_source(NT, ND, &consts);
+            if (which == 0) bytes.assign(src.c_str(), src.c_str() + src.size() + 1);
+            else bytes.assign(reinterpret_cast<const char*>(consts.data()), reinterpret_cast<const char*>(consts.data() + consts.size()));
+        }
+        if (bytes.empty() || (which == 0 && bytes.size() == 1)) throw NotImplementedError(std::string("no generated kernels for model family ") + m->family());
+        if (buf) std::memcpy(buf, bytes.data(), (size_t)std::min<unsigned long long>(*nbytes, bytes.size()));
+        *nbytes = bytes.size();
+    });
+}
 int teqpb200_device_count(void) {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }

@@ -108,6 +108,10 @@ public:
     // reducing functions (teqpcpp.hpp get_reducing_density / get_reducing_temperature); host, single composition
     virtual bool reducing(const double*, int, double*, double*) const { return false; }
     virtual std::string meta() const { return "{}"; }
+    // families whose kernels are generated per model (tq_gerg_jit.hpp): the generated translation unit + its constant pool, and the
+    // compiled cubin (no device needed: used by the CPU test tier and by tools/ to inspect the SASS)
+    virtual std::string jit_source(int, int, std::vector<double>*) const { return std::string(); }
+    virtual std::vector<char> jit_cubin(int, int) const { return {}; }
     // the POD parameter block the kernels receive (test harnesses replay the per-point device functions on it)
     virtual const void* params_blob(size_t* nbytes) const = 0;
 };

@@ -7,9 +7,13 @@
 #include <map>
 #include <tuple>
 
+#include <cstdlib>
+#include <mutex>
+
 #include "tq_common.hpp"
 #include "tq_gerg.cuh"
 #include "tq_gerg_iso.cuh"
+#include "tq_gerg_jit.hpp"
 
 namespace tq {
 void gergjet_launch_isoprops(const GergProgram&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
@@ -81,16 +85,12 @@ double binom_real(double a, int m) {
     return r;
 }
 
-struct RawTerm {
-    int w;       // weight index
-    double n, t;
-    int kind, d, l;
-    double c, eta, eps, beta, gamma;
-};
+using RawTerm = GergTerm;  // tq_gerg_jit.hpp
 
 class GergModel final : public Model {
 public:
     GergProgram P{};
+    GergSource src;  // the term list the per-model kernels are generated from (tq_gerg_jit.hpp)
     std::vector<std::string> names;
     double Rgas = 8.314472;  // GERG.hpp:1175 (2008), :906 (2004)
     std::string fam;
@@ -118,8 +118,41 @@ public:
     }
     // the compiled shapes; out is laid out for the REQUESTED (NT, ND), so a wider kernel writes through a scratch-free
     // remap only when shapes match exactly -- otherwise the caller (capi) asks for a compiled shape and slices.
+    // ---- per-model specialised kernels (NVRTC), one per derivative shape, compiled at first use and kept for the model's lifetime ----
+    struct Jit { JitSource s; JitKernel* k = nullptr; };
+    mutable std::mutex jit_mtx;
+    mutable std::map<std::pair<int, int>, Jit> jit;
+    ~GergModel() override { for (auto& [key, j] : jit) jit_release(j.k); }
+    static bool shape_ok(int NT, int ND) { return (NT == 0 && ND <= kMaxDerivD) || (ND == 0 && NT <= kMaxDerivT) || (NT <= 2 && ND <= 4); }
+    const Jit& specialised(int NT, int ND) const {
+        std::lock_guard<std::mutex> g(jit_mtx);
+        Jit& j = jit[{NT, ND}];
+        if (!j.k) {
+            j.s = gerg_generate(src, NT, ND);
+            j.k = jit_compile(j.s.code, "tqj_kernel", nullptr, nullptr, true);
+        }
+        return j;
+    }
+    std::string jit_source(int NT, int ND, std::vector<double>* consts) const override {
+        JitSource s = gerg_generate(src, NT, ND);
+        if (consts) *consts = s.consts;
+        return s.code;
+    }
+    std::vector<char> jit_cubin(int NT, int ND) const override {
+        std::vector<char> cubin;
+        jit_compile(gerg_generate(src, NT, ND).code, "tqj_kernel", nullptr, &cubin, false);
+        return cubin;
+    }
     void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override {
         if (in.npts == 0) return;
+        if (NT < 0 || ND < 0 || !shape_ok(NT, ND))
+            throw InvalidArgument("derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is not a supported shape for " + fam);
+        static const bool interp = std::getenv("TEQPB200_GERG_INTERPRETER") != nullptr;  // A/B measurements only (profiles/)
+        if (!interp) {
+            const Jit& j = specialised(NT, ND);
+            jit_launch_table(j.k, j.s.consts, j.s.w_in_smem ? (size_t)j.s.nw * 128 * sizeof(double) : 0, in, out, st);
+            return;
+        }
 #define TQ_CASE(a, b) if (NT == a && ND == b) { launch<a, b>(in, out, st); return; }
         TQ_CASE(0, 0) TQ_CASE(0, 1) TQ_CASE(0, 2) TQ_CASE(0, 3) TQ_CASE(0, 4) TQ_CASE(0, 5) TQ_CASE(0, 6)
         TQ_CASE(1, 0) TQ_CASE(2, 0) TQ_CASE(3, 0) TQ_CASE(4, 0)
@@ -198,6 +231,14 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         }
     }
     P.npair = pidx; P.ndep = ndep; P.nw = (int)N + ndep;
+    {
+        GergSource& S = m->src;
+        S.nc = (int)N; S.ndep = ndep;
+        S.Tc.assign(P.Tc, P.Tc + N); S.vc.assign(P.vc, P.vc + N);
+        S.pair.assign(P.pair, P.pair + pidx);
+        for (int q = 0; q < ndep; ++q) { S.dep_i.push_back(P.dep_i[q]); S.dep_j.push_back(P.dep_j[q]); S.depF.push_back(P.depF[q]); }
+        S.terms = raw;
+    }
 
     // group by density shape, then by tau exponent
     // key = (exponent shape h, then d): groups that share h are consecutive, d ascending (running product of delta)

@@ -94,3 +94,49 @@ def isochoric(spec, T, rhovec, hess=True):
     if rc:
         raise RuntimeError(err.value.decode())
     return f, g, H, lnphi, phi
+
+
+# ---- generated per-model kernels (csrc/tq_gerg_codegen.cu): the SAME translation unit NVRTC compiles for the GPU, compiled here with
+# g++ and run as a host loop, so the CPU tier checks the generated mathematics against the oracle ----------------------------------
+_JIT_CACHE = {}
+
+
+def jit_ar_table(spec, NT, ND, T, rho, x):
+    import hashlib
+    import subprocess
+    import tempfile
+    import teqp_b200
+    key = (json.dumps(spec, sort_keys=True), NT, ND)
+    if key not in _JIT_CACHE:
+        m = teqp_b200.make_model(spec)
+        L = teqp_b200.lib()
+
+        def fetch(which):
+            n = C.c_ulonglong(0); err = C.create_string_buffer(2000)
+            rc = L.teqpb200_generated_kernel(m._uuid, C.c_int(NT), C.c_int(ND), C.c_int(which), None, C.byref(n), err, C.c_int(2000))
+            if rc:
+                raise RuntimeError(err.value.decode())
+            buf = C.create_string_buffer(n.value)
+            rc = L.teqpb200_generated_kernel(m._uuid, C.c_int(NT), C.c_int(ND), C.c_int(which), buf, C.byref(n), err, C.c_int(2000))
+            if rc:
+                raise RuntimeError(err.value.decode())
+            return buf.raw[:n.value]
+        src = fetch(0).rstrip(b"\0")
+        consts = np.frombuffer(fetch(1), dtype=np.float64).copy()
+        d = os.path.join(tempfile.gettempdir(), "tqj_emul")
+        os.makedirs(d, exist_ok=True)
+        h = hashlib.sha1(src).hexdigest()[:16]
+        so = os.path.join(d, h + ".so")
+        if not os.path.exists(so):
+            cpp = os.path.join(d, h + ".cpp")
+            open(cpp, "wb").write(src)
+            subprocess.run(["g++", "-std=c++17", "-O1", "-mfma", "-fPIC", "-shared", "-w", cpp, "-o", so + ".tmp"], check=True)
+            os.replace(so + ".tmp", so)
+        _JIT_CACHE[key] = (C.CDLL(so), consts)
+    lib_, consts = _JIT_CACHE[key]
+    T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64); x = np.ascontiguousarray(x, dtype=np.float64)
+    n = T.size
+    bc = x.ndim == 1
+    out = np.empty(((NT + 1) * (ND + 1), n))
+    lib_.tqj_host(_p(consts), C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_longlong(1 if bc else n), C.c_int(1 if bc else 0), _p(out))
+    return out.reshape(NT + 1, ND + 1, n)

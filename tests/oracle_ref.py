@@ -150,3 +150,73 @@ class RefModel:
         out = np.empty((nc * nc if what == 3 else nc, n))
         self._call(lib().ref_lnphi_family, C.c_int(what), C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), _p(out))
         return out
+
+
+def _two_sum_split(v):
+    """double -> (hi, lo) pair; here lo = 0 (helper for truth_alphar_dd callers that perturb in quad)"""
+    v = np.ascontiguousarray(v, dtype=np.float64)
+    return v, np.zeros_like(v)
+
+
+class TruthModel:
+    """The reference's model templates in __float128 (oracle/ref_truth.cpp): the adjudicator between libteqpb200 and RefModel."""
+
+    def __init__(self, spec):
+        self.spec = spec if isinstance(spec, str) else json.dumps(spec)
+        L = lib()
+        L.truth_build_model.restype = C.c_void_p
+        L.truth_build_model.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        L.truth_free_model.argtypes = [C.c_void_p]
+        err = C.create_string_buffer(2000)
+        self.h = L.truth_build_model(self.spec.encode(), err, 2000)
+        if not self.h:
+            raise RuntimeError("truth oracle: " + err.value.decode())
+        self.nthreads = os.cpu_count() or 1
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().truth_free_model(C.c_void_p(self.h))
+            self.h = None
+
+    _call = RefModel._call
+
+    def ar_table(self, NT, ND, T, rho, x):
+        """Lambda_nm, n <= NT, m <= ND -> [NT+1][ND+1][npts]; shapes (0,6), (4,0), (2,4)"""
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n)
+        out = np.empty(((NT + 1) * (ND + 1), n))
+        self._call(lib().truth_ar_table, C.c_int(NT), C.c_int(ND), C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out.reshape(NT + 1, ND + 1, n)
+
+    def Ar0n_refdriver(self, nmax, T, rho, x):
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n)
+        out = np.empty((nmax + 1, n))
+        self._call(lib().truth_Ar0n_refdriver, C.c_int(nmax), C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
+    def ATrhoXi_table(self, T, rho, x):
+        """[ncomp][3][3][4][npts], same layout as Model.get_ATrhoXi_table_batch"""
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n); nc = x.shape[0]
+        out = np.empty((nc * 36, n))
+        self._call(lib().truth_ATrhoXi_table, C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(nc), _p(out))
+        return out.reshape(nc, 3, 3, 4, n)
+
+    def fgradHessian(self, T, rhovec, want_H=True):
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        n = T.size; rv = _soa(rhovec, n); nc = rv.shape[0]
+        f = np.empty(n); g = np.empty((nc, n)); H = np.empty((nc * nc, n)) if want_H else None
+        self._call(lib().truth_Psir_fgradHessian, C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), _p(f), _p(g), _p(H) if want_H else None)
+        return f, g, H
+
+    def alphar_dd(self, T, rho, x):
+        """alphar at (T, rho, x) given as (hi, lo) double-double pairs; returns (hi, lo) of the quad result"""
+        (Th, Tl), (rh, rl), (xh, xl) = T, rho, x
+        Th = np.ascontiguousarray(Th, dtype=np.float64); n = Th.size
+        arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (Th, Tl, rh, rl)]
+        xh = _soa(xh, n); xl = _soa(xl, n)
+        oh = np.empty(n); ol = np.empty(n)
+        self._call(lib().truth_alphar_dd, C.c_longlong(n), _p(arrs[0]), _p(arrs[1]), _p(arrs[2]), _p(arrs[3]), _p(xh), _p(xl), C.c_int(xh.shape[0]),
+                   _p(oh), _p(ol))
+        return oh, ol
