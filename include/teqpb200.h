@@ -106,6 +106,10 @@ int teqpb200_set_stream(void* cuda_stream);                 /* stream for TEQPB2
 void* teqpb200_host_alloc(unsigned long long nbytes);       /* pinned host memory */
 void teqpb200_host_free(void* p);
 long long int teqpb200_kernel_launches(void);               /* kernels launched by this library so far (all threads) */
+int teqpb200_release_scratch(void);                         /* frees the device staging arenas of the host-pointer path */
+void teqpb200_inject_fault(const long long int chunk_index); /* TEST HOOK: the chunk_index-th staged chunk from now on fails (error-path tests) */
+double teqpb200_last_call_device_ms(const int device);      /* device-side duration (first H2D .. last D2H, CUDA events) of the last
+                                                               host-pointer call on that device; -1 if none */
 int teqpb200_fp64_peak(double* tflops, char* errmsg, int errmsg_length); /* measured DFMA peak of the current device, TFLOP/s */
 /* deterministic synthetic state points on the device: counter-hash uniforms u_j(k) of the global point
    index k0+k; T = Tlo + (Thi-Tlo) u0, rho log-uniform in [rholo, rhohi] from u1, x_i ~ z0_i exp(0.2 (2 u_{2+i} - 1)) renormalised.

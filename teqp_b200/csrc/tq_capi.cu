@@ -97,24 +97,55 @@ using ChunkFn = std::function<void(long long n, const std::vector<const double*>
 constexpr int kSlots = 3;
 constexpr long long kMaxChunk = 1LL << 22;
 constexpr long long kMinChunk = 1LL << 16;
+constexpr size_t kMaxSlotBytes = 384ull << 20;  // scratch per (device, slot): wide outputs (GERG21 tables, ~800 rows) shrink the chunk instead
 
-struct DeviceArena {  // grow-only device scratch, one per (device, slot)
+struct DeviceArena {  // grow-only device scratch, one per (device, slot); released by teqpb200_release_scratch()
     double* p = nullptr; size_t cap = 0; cudaStream_t st = nullptr;
 };
-std::mutex g_run_mtx;
-std::unordered_map<int, std::array<DeviceArena, kSlots>> g_arenas;
+struct DeviceState {  // one per device: concurrent host-pointer calls serialise per device, not process-wide
+    std::mutex mtx;
+    std::array<DeviceArena, kSlots> arenas;
+};
+std::mutex g_state_mtx;
+std::unordered_map<int, std::unique_ptr<DeviceState>> g_states;
+std::atomic<long long> g_fault_chunk{-1};   // test hook (teqpb200_inject_fault): the chunk with this running index fails
+std::atomic<long long> g_chunk_counter{0};
+// device-side time of the last host-pointer call, per device: first H2D enqueued -> last D2H finished (CUDA events on the arena streams)
+std::mutex g_time_mtx;
+std::unordered_map<int, double> g_last_ms;
+DeviceState& device_state(int dev) {
+    std::lock_guard<std::mutex> g(g_state_mtx);
+    auto& p = g_states[dev];
+    if (!p) p = std::make_unique<DeviceState>();
+    return *p;
+}
+
+// rows are contiguous n-double spans at p + r*npts + offset: one plain async copy per row (cudaMemcpy2DAsync rejects host pitches
+// above cudaDevAttrMaxPitch = 2^31-1 bytes, i.e. batches above 2.68e8 points)
+void copy_rows_h2d(double* dst, long long dst_stride, const double* src, long long src_stride, long long n, int rows, cudaStream_t st) {
+    for (int r = 0; r < rows; ++r)
+        TQ_CUDA(cudaMemcpyAsync(dst + (size_t)r * dst_stride, src + (size_t)r * src_stride, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, st));
+}
+void copy_rows_d2h(double* dst, long long dst_stride, const double* src, long long src_stride, long long n, int rows, cudaStream_t st) {
+    for (int r = 0; r < rows; ++r)
+        TQ_CUDA(cudaMemcpyAsync(dst + (size_t)r * dst_stride, src + (size_t)r * src_stride, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, st));
+}
 
 void run_on_device(int dev, long long k0, long long n_dev, long long npts, const std::vector<HostIn>& ins,
                    const std::vector<HostOut>& outs, const ChunkFn& fn) {
     if (n_dev <= 0) return;
     TQ_CUDA(cudaSetDevice(dev));
-    auto& arenas = g_arenas[dev];
+    DeviceState& S = device_state(dev);
+    std::lock_guard<std::mutex> lock(S.mtx);
+    auto& arenas = S.arenas;
+    size_t rows_chunk = 0, fixed = 0;   // rows that scale with the chunk; doubles that do not (broadcast inputs)
+    for (auto& a : ins) { if (a.broadcast) fixed += a.rows; else rows_chunk += a.rows; }
+    for (auto& a : outs) rows_chunk += a.rows;
     long long chunk = std::min(kMaxChunk, std::max(kMinChunk, (n_dev + 7) / 8));
+    const long long by_bytes = (long long)(kMaxSlotBytes / (sizeof(double) * std::max<size_t>(1, rows_chunk)));
+    chunk = std::min(chunk, std::max<long long>(4096, by_bytes & ~127LL));
     chunk = std::min(chunk, n_dev);
-    size_t rows_total = 0;
-    for (auto& a : ins) rows_total += a.rows;
-    for (auto& a : outs) rows_total += a.rows;
-    const size_t need = rows_total * (size_t)chunk * sizeof(double);
+    const size_t need = (rows_chunk * (size_t)chunk + fixed) * sizeof(double);
     for (int s = 0; s < kSlots; ++s) {
         DeviceArena& A = arenas[s];
         if (!A.st) TQ_CUDA(cudaStreamCreateWithFlags(&A.st, cudaStreamNonBlocking));
@@ -124,43 +155,66 @@ void run_on_device(int dev, long long k0, long long n_dev, long long npts, const
             A.cap = need;
         }
     }
-    int slot = 0;
-    for (long long c0 = 0; c0 < n_dev; c0 += chunk, slot = (slot + 1) % kSlots) {
-        const long long n = std::min(chunk, n_dev - c0);
-        DeviceArena& A = arenas[slot];
-        cudaStream_t st = A.st;
-        double* cur = A.p;
-        std::vector<const double*> din; std::vector<double*> dout;
-        for (auto& a : ins) {
-            din.push_back(cur);
-            if (a.broadcast) {
-                TQ_CUDA(cudaMemcpyAsync(cur, a.p, sizeof(double) * a.rows, cudaMemcpyHostToDevice, st));
-            } else {
-                TQ_CUDA(cudaMemcpy2DAsync(cur, sizeof(double) * n, a.p + k0 + c0, sizeof(double) * npts, sizeof(double) * n, a.rows, cudaMemcpyHostToDevice, st));
+    cudaEvent_t ev0 = nullptr, ev1[kSlots] = {nullptr, nullptr, nullptr};
+    TQ_CUDA(cudaEventCreate(&ev0));
+    for (int s = 0; s < kSlots; ++s) TQ_CUDA(cudaEventCreate(&ev1[s]));
+    auto drop_events = [&] { cudaEventDestroy(ev0); for (int s = 0; s < kSlots; ++s) cudaEventDestroy(ev1[s]); };
+    try {
+        int slot = 0;
+        TQ_CUDA(cudaEventRecord(ev0, arenas[0].st));
+        for (long long c0 = 0; c0 < n_dev; c0 += chunk, slot = (slot + 1) % kSlots) {
+            const long long n = std::min(chunk, n_dev - c0);
+            DeviceArena& A = arenas[slot];
+            cudaStream_t st = A.st;
+            double* cur = A.p;
+            if (g_chunk_counter++ == g_fault_chunk.load()) { g_fault_chunk = -1; throw DeviceError("injected fault (teqpb200_inject_fault)"); }
+            std::vector<const double*> din; std::vector<double*> dout;
+            for (auto& a : ins) {
+                din.push_back(cur);
+                if (a.broadcast) {
+                    TQ_CUDA(cudaMemcpyAsync(cur, a.p, sizeof(double) * a.rows, cudaMemcpyHostToDevice, st));
+                    cur += a.rows;
+                } else {
+                    copy_rows_h2d(cur, n, a.p + k0 + c0, npts, n, a.rows, st);
+                    cur += (size_t)a.rows * chunk;
+                }
             }
-            cur += (size_t)a.rows * chunk;
+            for (auto& a : outs) { dout.push_back(cur); cur += (size_t)a.rows * chunk; }
+            fn(n, din, dout, st);
+            for (size_t q = 0; q < outs.size(); ++q) {
+                if (!outs[q].p) continue;
+                copy_rows_d2h(outs[q].p + k0 + c0, npts, dout[q], n, n, outs[q].rows, st);
+            }
         }
-        for (auto& a : outs) { dout.push_back(cur); cur += (size_t)a.rows * chunk; }
-        fn(n, din, dout, st);
-        for (size_t q = 0; q < outs.size(); ++q) {
-            if (!outs[q].p) continue;
-            TQ_CUDA(cudaMemcpy2DAsync(outs[q].p + k0 + c0, sizeof(double) * npts, dout[q], sizeof(double) * n, sizeof(double) * n, outs[q].rows, cudaMemcpyDeviceToHost, st));
-        }
+    } catch (...) {
+        // copies into the caller's buffers may still be queued: drain them before the error leaves the library
+        for (int s = 0; s < kSlots; ++s) if (arenas[s].st) cudaStreamSynchronize(arenas[s].st);
+        cudaGetLastError();
+        drop_events();
+        throw;
     }
+    for (int s = 0; s < kSlots; ++s) TQ_CUDA(cudaEventRecord(ev1[s], arenas[s].st));
     for (int s = 0; s < kSlots; ++s) TQ_CUDA(cudaStreamSynchronize(arenas[s].st));
+    float ms = 0.f, m = 0.f;
+    for (int s = 0; s < kSlots; ++s) if (cudaEventElapsedTime(&m, ev0, ev1[s]) == cudaSuccess) ms = std::max(ms, m);
+    { std::lock_guard<std::mutex> g(g_time_mtx); g_last_ms[dev] = ms; }
+    drop_events();
 }
 
 void run_host(long long npts, const std::vector<HostIn>& ins, const std::vector<HostOut>& outs, const ChunkFn& fn) {
     if (npts <= 0) return;
-    std::lock_guard<std::mutex> g(g_run_mtx);
     std::vector<int> devs;
     { std::lock_guard<std::mutex> gd(g_dev_mtx); devs = g_devices; }
     int cur = 0;
     TQ_CUDA(cudaGetDevice(&cur));
     if (devs.empty() || npts < (long long)devs.size() * 1024) devs = {devs.empty() ? cur : devs[0]};
     const int nd = (int)devs.size();
-    for (int d : devs) (void)g_arenas[d];  // create the map entries before any worker thread touches the map
-    if (nd == 1) { run_on_device(devs[0], 0, npts, npts, ins, outs, fn); TQ_CUDA(cudaSetDevice(cur)); return; }
+    if (nd == 1) {
+        try { run_on_device(devs[0], 0, npts, npts, ins, outs, fn); }
+        catch (...) { cudaSetDevice(cur); throw; }
+        TQ_CUDA(cudaSetDevice(cur));
+        return;
+    }
     // contiguous even split, remainder to the last device; one host thread per device
     const long long per = npts / nd;
     std::vector<std::thread> th;
@@ -174,9 +228,9 @@ void run_host(long long npts, const std::vector<HostIn>& ins, const std::vector<
             catch (const std::exception& e) { codes[d] = 9999; errs[d] = e.what(); }
         });
     }
-    for (auto& t : th) t.join();
+    for (auto& t : th) t.join();   // every device has drained its streams (run_on_device syncs on both exits) before an error is reported
     TQ_CUDA(cudaSetDevice(cur));
-    for (int d = 0; d < nd; ++d) if (codes[d]) throw Error(codes[d], errs[d]);
+    for (int d = 0; d < nd; ++d) if (codes[d]) throw Error(codes[d], "device " + std::to_string(devs[d]) + ": " + errs[d]);
 }
 
 // one entry point for both pointer kinds
@@ -528,6 +582,30 @@ void* teqpb200_host_alloc(unsigned long long nbytes) {
 }
 void teqpb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 long long int teqpb200_kernel_launches(void) { return g_launches.load(); }
+int teqpb200_release_scratch(void) {
+    // frees the per-device staging arenas of the host-pointer path (they only grow otherwise); safe between calls
+    std::lock_guard<std::mutex> g(g_state_mtx);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (auto& [dev, S] : g_states) {
+        std::lock_guard<std::mutex> l(S->mtx);
+        cudaSetDevice(dev);
+        for (auto& A : S->arenas) {
+            if (A.st) cudaStreamSynchronize(A.st);
+            if (A.p) cudaFree(A.p);
+            A.p = nullptr; A.cap = 0;
+        }
+    }
+    cudaSetDevice(cur);
+    cudaGetLastError();
+    return 0;
+}
+void teqpb200_inject_fault(const long long int chunk_index) { g_chunk_counter = 0; g_fault_chunk = chunk_index; }
+double teqpb200_last_call_device_ms(const int device) {
+    std::lock_guard<std::mutex> g(g_time_mtx);
+    auto it = g_last_ms.find(device);
+    return it == g_last_ms.end() ? -1.0 : it->second;
+}
 
 }  // extern "C"
 

@@ -128,13 +128,15 @@ class Model:
                                                  C.c_int(nc), ao.ptr, C.c_int(flags), err, C.c_int(2000)), err)
         return ao.obj
 
-    def _iso(self, fn, T, rhovec, nrows_list):
+    def _iso(self, fn, T, rhovec, nrows_list, out=None):
         dev = _is_torch(T)
         flags = DEVICE_PTRS if dev else 0
         n = int(T.numel() if dev else np.size(T))
         nc = rhovec.shape[0]
         aT, av = _Arg(T, dev), _Arg(rhovec, dev)
-        outs = [_Arg(self._out((r, n) if r > 1 or True else (n,), dev, T), dev) for r in nrows_list]
+        if out is not None and not isinstance(out, (tuple, list)):
+            out = (out,)
+        outs = [_Arg(self._out((r, n), dev, T, None if out is None else out[q]), dev) for q, r in enumerate(nrows_list)]
         err = C.create_string_buffer(2000)
         self._enter(dev)
         _check(fn(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *[o.ptr for o in outs], C.c_int(flags), err, C.c_int(2000)), err)
@@ -159,16 +161,17 @@ class Model:
         _check(lib().isochoric_properties_batch(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *ptrs, C.c_int(flags), err, C.c_int(2000)), err)
         return {k: (outs[k].obj[0] if rows[k] == 1 else outs[k].obj) for k in which}
 
-    def build_Psir_fgradHessian_batch(self, T, rhovec):
+    def build_Psir_fgradHessian_batch(self, T, rhovec, out=None):
+        """returns (Psir[npts], grad[Ncomp][npts], H[Ncomp][Ncomp][npts]); out = (f[1][npts], g[Ncomp][npts], H[Ncomp*Ncomp][npts]) reuses buffers"""
         nc = rhovec.shape[0]
-        f, g, H = self._iso(lib().build_Psir_fgradHessian_batch, T, rhovec, [1, nc, nc * nc])
+        f, g, H = self._iso(lib().build_Psir_fgradHessian_batch, T, rhovec, [1, nc, nc * nc], out)
         return f[0], g, H.reshape((nc, nc) + tuple(H.shape[1:]))
 
-    def get_ln_fugacity_coefficients_batch(self, T, rhovec):
-        return self._iso(lib().get_ln_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]])[0]
+    def get_ln_fugacity_coefficients_batch(self, T, rhovec, out=None):
+        return self._iso(lib().get_ln_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]], out)[0]
 
-    def get_fugacity_coefficients_batch(self, T, rhovec):
-        return self._iso(lib().get_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]])[0]
+    def get_fugacity_coefficients_batch(self, T, rhovec, out=None):
+        return self._iso(lib().get_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]], out)[0]
 
     # ------------------------------------------------------------------ reference scalar surface
     def get_R(self, molefrac):

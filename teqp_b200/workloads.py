@@ -42,8 +42,14 @@ def synth_points(npts, k0, Tlo, Thi, rholo, rhohi, z0, seed=SEED):
 # AGA8 natural-gas compositions used by the reference's GERG tests (src/tests/catch_test_GERG.cxx:136 and :130), mole percent
 _C3_NAMES = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "isobutane", "n-butane", "isopentane", "n-pentane", "n-hexane"]
 _C3_Z = [96.370276, 0.291926, 0.298014, 1.400282, 0.780001, 0.14425, 0.460146, 0.0759, 0.0549, 0.124306]
-_GERG21 = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "n-butane", "isobutane", "n-pentane", "isopentane", "n-hexane",
-           "n-heptane", "n-octane", "hydrogen", "oxygen", "carbonmonoxide", "water", "helium", "argon", "hydrogensulfide", "n-nonane", "n-decane"]
+# C5: all 21 GERG-2008 components in the component order of the AGA8 test code (src/tests/catch_test_GERG.cxx:512) with the AGA8 gas row of
+# catch_test_GERG.cxx:130 (mole percent; 15 of 21 non-zero).  SURVEY.md section 8d: the zeros become 1e-4 (mole fraction) before
+# renormalising so that the Hessian / d ln phi / dx are defined; the trace components are where H_ij/x_i loses digits.
+_GERG21 = ["methane", "nitrogen", "carbondioxide", "ethane", "propane", "isobutane", "n-butane", "isopentane", "n-pentane", "n-hexane",
+           "n-heptane", "n-octane", "n-nonane", "n-decane", "hydrogen", "oxygen", "carbonmonoxide", "water", "hydrogensulfide", "helium", "argon"]
+_C5_ROW = [98.110602, 0.813399, 0.1209, 0.611199, 0.2153, 0.0339, 0.0453, 0.0115, 0.00925, 0.006, 0.0061, 0.0028, 0.0003, 0.00005, 0, 0, 0, 0, 0,
+           0.0134, 0]
+_C5_Z = [v / 100.0 if v != 0 else 1e-4 for v in _C5_ROW]
 
 
 # C4: methane + ethane (library values) + water (Dufal-2015 values, src/tests/catch_test_SAFTgeneric.cxx:104-128) + methane + ethane (library values,
@@ -74,7 +80,7 @@ def _norm(z):
 WORKLOADS = {
     # C1: Peng-Robinson pure methane (values of src/tests/catch_test_cubics.cxx:28-30), Ar00..Ar04
     "C1": dict(spec={"kind": "PR", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011]}},
-               T=(100.0, 600.0), rho=(1.0, 25000.0), z0=[1.0], npts=10**6, what="Ar0n", nmax=4, bytes_per_point=56),
+               T=(100.0, 600.0), rho=(1.0, 25000.0), z0=[1.0], npts=10**6, what="Ar0n", nmax=4, bytes_per_point=56, bound="hbm"),
     # C2: PC-SAFT methane + ethane (library values, include/teqp/models/pcsaft.hpp:53-54)
     "C2": dict(spec={"kind": "PCSAFT", "model": {"names": ["Methane", "Ethane"]}},
                T=(150.0, 450.0), rho=(1.0, 20000.0), z0=[0.5, 0.5], npts=10**7, what="Arxy+lnphi", bytes_per_point=96),
@@ -83,9 +89,10 @@ WORKLOADS = {
                T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm(_C3_Z), npts=10**8, what="Ar0n", nmax=4, bytes_per_point=136),
     # C4: SAFT-VR-Mie ternary with Dufal association on water: the get_ATrhoXi table (23 combinations x 3 components)
     "C4": dict(spec=_C4_SPEC, T=(280.0, 500.0), rho=(10.0, 30000.0), z0=[0.3, 0.3, 0.4], npts=10**7, what="ATrhoXi", bytes_per_point=40 + 8 * 108),
-    # C5 (Ar0n variant): GERG-2008 all 21 components
+    # C5: GERG-2008 all 21 components, isochoric Hessian / fugacity composition derivatives; 10^6 points per GPU (weak), 8*10^6 total (strong)
     "C5": dict(spec={"kind": "GERG2008resid", "model": {"names": _GERG21}},
-               T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm([1.0] * 21), npts=10**6, what="Ar0n", nmax=4, bytes_per_point=224),
+               T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm(_C5_Z), npts=10**6, npts_strong=8 * 10**6, what="fgradHessian", nmax=4,
+               bytes_per_point=8 * 22 + 8 * (1 + 21 + 441)),
 }
 
 

@@ -20,6 +20,10 @@ class EmulBackend:
         self.e = emul
 
     def ar_table(self, spec, NT, ND, T, rho, x):
+        if spec["kind"].startswith("GERG") and T.size:
+            # the product evaluates GERG tables with the per-model GENERATED kernel: replay that source (compiled for the host) -- the
+            # interpreter kernel's per-point function is replayed as well and must agree to the parity rule
+            return self.e.jit_ar_table(spec, NT, ND, T, rho, x)
         return self.e.ar_table(spec, NT, ND, T, rho, x)
 
     def ATrhoXi_table(self, spec, T, rho, x):

@@ -132,3 +132,74 @@ def test_reference_c_abi_scalar_calls(be, oracle):
     np.testing.assert_allclose(v, r, rtol=1e-12)
     assert m.get_Ar11(300.0, 3000.0, [0.4, 0.6]) == pytest.approx(ref.ArNM(1, 1, np.array([300.0]), np.array([3000.0]), np.array([[0.4], [0.6]]))[0], rel=1e-12)
     assert m.get_R([0.4, 0.6]) == 8.31446261815324
+
+
+def test_library_sharder_bit_identical(be):
+    """north_star (c) / SURVEY 8e: the library's own host driver (teqpb200_set_devices + a host-pointer call) splits the batch over the
+    configured devices; the concatenated result must be bit-identical to the single-device result.  [0, 0] exercises the split, the
+    per-device threads and the offsets on a one-GPU box; [0, 1] and all devices run where the box has them."""
+    import teqp_b200
+    nd = teqp_b200.device_count()
+    spec, T, rho, x = cases.points("GERG10", 300007)
+    m = be.model(spec)
+    teqp_b200.set_devices([])
+    one = m.get_Ar0n_batch(4, T, rho, x)
+    layouts = [[0], [0, 0], [0, 0, 0]]
+    if nd >= 2:
+        layouts += [[0, 1], [1, 0]]
+    if nd > 2:
+        layouts.append(list(range(nd)))
+    try:
+        for ids in layouts:
+            teqp_b200.set_devices(ids)
+            got = m.get_Ar0n_batch(4, T, rho, x)
+            assert np.array_equal(got, one), "sharded over %s differs from the single-device result" % ids
+            rv = np.ascontiguousarray(x[:, :20011] * rho[:20011])
+            f1, g1, H1 = m.build_Psir_fgradHessian_batch(T[:20011].copy(), rv)
+        teqp_b200.set_devices([])
+        f0, g0, H0 = m.build_Psir_fgradHessian_batch(T[:20011].copy(), rv)
+        assert np.array_equal(H0, H1) and np.array_equal(g0, g1) and np.array_equal(f0, f1)
+    finally:
+        teqp_b200.set_devices([])
+
+
+def test_host_driver_error_path(be):
+    """a failure in the middle of a host-pointer batch: the call returns an error (no exception crosses the ABI), nothing is left queued
+    on the caller's buffers, and the next call on the same handle is correct"""
+    import teqp_b200
+    lib = teqp_b200.lib()
+    spec, T, rho, x = cases.points("GERG10", 400000)
+    m = be.model(spec)
+    good = m.get_Ar0n_batch(4, T, rho, x)
+    for ids in ([], [0, 0]):
+        teqp_b200.set_devices(ids)
+        try:
+            lib.teqpb200_inject_fault(C.c_longlong(2))
+            with pytest.raises(teqp_b200.TeqpError) as ei:
+                m.get_Ar0n_batch(4, T, rho, x)
+            assert "injected fault" in str(ei.value)
+            again = m.get_Ar0n_batch(4, T, rho, x)
+            assert np.array_equal(again, good)
+        finally:
+            lib.teqpb200_inject_fault(C.c_longlong(-1))
+            teqp_b200.set_devices([])
+    assert lib.teqpb200_release_scratch() == 0
+    assert np.array_equal(m.get_Ar0n_batch(4, T, rho, x), good)
+
+
+def test_large_host_batch_rows_over_2GiB_pitch(be):
+    """host batches whose row pitch exceeds cudaDevAttrMaxPitch (2^31-1 bytes = 2.68e8 points) used to be rejected by the 2-D copies; the
+    driver now copies row by row.  3e8 points of a pure cubic (T, rho, one x row in; Ar00, Ar01 out = 12 GB of host memory)"""
+    import psutil
+    if psutil.virtual_memory().available < 48 * 2**30:
+        pytest.skip("needs ~12 GB of host memory with headroom")
+    n = 300_000_000
+    spec = cases.SPECS["PR1"][0]
+    m = be.model(spec)
+    T = np.full(n, 300.0); rho = np.full(n, 5000.0); x = np.ones(1)
+    T[-1] = 250.0; rho[-1] = 123.0
+    out = m.get_Ar0n_batch(1, T, rho, x)
+    a = m.get_Ar0n_batch(1, T[:4].copy(), rho[:4].copy(), x)
+    b = m.get_Ar0n_batch(1, T[-4:].copy(), rho[-4:].copy(), x)
+    assert np.array_equal(out[:, :4], a) and np.array_equal(out[:, -4:], b)
+    assert np.all(out[:, 1:-1] == out[:, :1])
