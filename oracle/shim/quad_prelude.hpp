@@ -15,6 +15,20 @@
 #include <limits>
 
 namespace std {
+// libstdc++ 13 has no numeric_limits<__float128>.  The reference uses epsilon() of the BASE type as an algorithmic constant: the cutoff of
+// the Barker-Henderson integral is where exp(-u/T) = EPS (saftvrmie.hpp:299-301).  The truth leg must evaluate the SAME formula the double
+// reference evaluates (same cutoff, same 10-point Gauss-Legendre interval), only in wider arithmetic, so epsilon() is the DOUBLE epsilon here;
+// with the binary128 epsilon the quadrature interval changes and the "truth" would be that of another formula (it moves d_ii by ~1e-7).
+template<> struct numeric_limits<__float128> {
+    static constexpr bool is_specialized = true, is_signed = true, is_integer = false, is_exact = false, has_infinity = true, has_quiet_NaN = true;
+    static constexpr int digits = 113, digits10 = 33, max_digits10 = 36, radix = 2;
+    static constexpr __float128 epsilon() noexcept { return 2.220446049250313080847263336181640625e-16Q; }
+    static constexpr __float128 min() noexcept { return 3.36210314311209350626267781732175260e-4932Q; }
+    static constexpr __float128 max() noexcept { return 1.18973149535723176508575932662800702e4932Q; }
+    static constexpr __float128 lowest() noexcept { return -1.18973149535723176508575932662800702e4932Q; }
+    static __float128 infinity() noexcept { return __builtin_huge_valq(); }
+    static __float128 quiet_NaN() noexcept { return __builtin_nanq(""); }
+};
 inline __float128 exp(__float128 x) { return expq(x); }
 inline __float128 log(__float128 x) { return logq(x); }
 inline __float128 log10(__float128 x) { return log10q(x); }

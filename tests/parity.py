@@ -1,6 +1,6 @@
 """The parity rule used by every test (DESIGN.md "Parity rule"):
 
-    |got - ref| <= RTOL * |ref| + RTOL * S ,   RTOL = 1e-12
+    |got - ref| <= RTOL * |ref| + FTOL * S ,   RTOL = 1e-12,  FTOL = 2e-14
 
 S is the absolute floor "near zero-valued derivatives" that BASELINE.json's north_star allows: the scale of the derivative
 family at that state point.  It is needed because (a) a derivative that crosses zero has no meaningful relative error, and
@@ -8,13 +8,20 @@ family at that state point.  It is needed because (a) a derivative that crosses 
 (e.g. Ar04 of a term ~ delta^1 is exactly 0 analytically but eps-sized in exp(d ln delta) arithmetic), so two correct
 implementations differ by that much.  Both the reference and the kernels work in TAYLOR-COEFFICIENT space
 (c_nm = Lambda_nm / (n! m!)), so the family scale is taken there: S_nm = n! m! max_ij |Lambda_ij| / (i! j!).
-The helper reports how often the floor was needed so a test can bound it."""
+FTOL is MEASURED, not chosen: tools/adjudicate.py compares the kernels and the double-precision oracle with the reference's own
+templates evaluated in binary128 (oracle/ref_truth.cpp); both sit 1e-15..5e-15 S from the exact value and <= 3e-15 S from each other
+for every Lambda_nm of C1..C5 (profiles/r02_truth_adjudication_*.json), so 2e-14 S leaves one order of magnitude and a regression
+50x smaller than what the round-1 floor (1e-12 S) let through now fails.  Every check records how many points needed the floor
+(REPORT; printed at the end of the test session) and bounds that fraction."""
 import numpy as np
 
 RTOL = 1e-12
+FTOL = 2e-14
+SIGNIFICANT = 1e-2   # a value below this fraction of its family scale counts as a "near zero-valued derivative"
+REPORT = []   # (name, points, fraction needing the floor, max |d|/S, limit, fraction needing the floor among significant values)
 
 
-def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=1.0):
+def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=0.02, ftol=FTOL):
     got = np.asarray(got, dtype=np.float64); ref = np.asarray(ref, dtype=np.float64)
     assert got.shape == ref.shape, (name, got.shape, ref.shape)
     fin_r, fin_g = np.isfinite(ref), np.isfinite(got)
@@ -25,14 +32,23 @@ def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=1.0):
     d = np.where(fin_r, np.abs(got - ref), 0.0)
     a = np.where(fin_r, np.abs(ref), 1.0)
     s = np.where(np.isfinite(scale), scale, 0.0)
-    tol = rtol * a + rtol * s
+    tol = rtol * a + ftol * s
     bad = d > tol
     if np.any(bad):
         i = np.unravel_index(np.argmax(d / np.maximum(tol, 1e-300)), d.shape)
         raise AssertionError("%s: %d of %d outside tolerance; worst at %s: got %.17g ref %.17g |d| %.3e tol %.3e"
                              % (name, int(bad.sum()), d.size, i, got[i], ref[i], d[i], tol[i]))
-    floor_frac = float(np.mean(d > rtol * a))
-    assert floor_frac <= max_floor_frac, "%s: %.3f of the points needed the absolute floor (limit %.3f)" % (name, floor_frac, max_floor_frac)
+    # How often was the floor needed?  Two fractions: over all points (reported), and over the points where the value is NOT a
+    # "near zero-valued derivative" -- |ref| >= SIGNIFICANT * S -- which is the one a test bounds: the floor exists for values that are
+    # small against their family (north_star), so needing it for a value that is not small is a real relative-accuracy miss.
+    need = d > rtol * a
+    floor_frac = float(np.mean(need)) if d.size else 0.0
+    sig = a >= SIGNIFICANT * s
+    floor_sig = float(np.mean(need & sig)) if d.size else 0.0
+    with np.errstate(divide="ignore", invalid="ignore"):
+        in_s = float(np.max(np.where(s > 0, d / s, 0.0))) if d.size else 0.0
+    REPORT.append((name, int(d.size), floor_frac, in_s, max_floor_frac, floor_sig))
+    assert floor_sig <= max_floor_frac, "%s: %.4f of the points needed the absolute floor although |ref| >= %.0e S (limit %.3f)" % (name, floor_sig, SIGNIFICANT, max_floor_frac)
     return floor_frac
 
 

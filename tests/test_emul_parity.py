@@ -39,3 +39,13 @@ def test_gerg_vs_aga8_golden(emul):
 
 def test_edge_cases(emul, oracle):
     ps.edge_cases(ps.EmulBackend(emul), oracle)
+
+
+@pytest.mark.parametrize("cfg,name,what", [("C1", "PR1", ("ar",)), ("C2", "PCSAFT2", ("ar", "iso")), ("C3", "GERG10", ("ar",)),
+                                           ("C4", "GSAFT_C4", ("ar", "atrhoxi")), ("C5", "GERG21", ("ar", "iso"))])
+def test_truth_adjudication(emul, oracle, cfg, name, what):
+    """the kernels are as close to the exact value of the reference's formulas (its own model templates evaluated in binary128,
+    oracle/ref_truth.cpp) as the double-precision reference is: |kernel - truth| <= k |oracle - truth| + 4 eps S on the max and the 99.9th
+    percentile of every output of the five BASELINE configs (k = 2; 3 for the SAFT-VR-Mie + association family)"""
+    rows, bad = ps.truth_adjudication(ps.EmulBackend(emul), oracle, name, n=300, what=what)
+    assert not bad, "%s: farther from the binary128 truth than the reference is: %s" % (cfg, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad])

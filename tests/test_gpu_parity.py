@@ -203,3 +203,13 @@ def test_large_host_batch_rows_over_2GiB_pitch(be):
     b = m.get_Ar0n_batch(1, T[-4:].copy(), rho[-4:].copy(), x)
     assert np.array_equal(out[:, :4], a) and np.array_equal(out[:, -4:], b)
     assert np.all(out[:, 1:-1] == out[:, :1])
+
+
+@pytest.mark.parametrize("cfg,name,what", [("C1", "PR1", ("ar",)), ("C2", "PCSAFT2", ("ar", "iso")), ("C3", "GERG10", ("ar",)),
+                                           ("C4", "GSAFT_C4", ("ar", "atrhoxi")), ("C5", "GERG21", ("ar", "iso"))])
+def test_truth_adjudication(be, oracle, cfg, name, what):
+    """the kernels are as close to the exact value of the reference's formulas (its own model templates evaluated in binary128,
+    oracle/ref_truth.cpp) as the double-precision reference is: |kernel - truth| <= k |oracle - truth| + 4 eps S on the max and the 99.9th
+    percentile of every output of the five BASELINE configs (k = 2; 3 for the SAFT-VR-Mie + association family)"""
+    rows, bad = ps.truth_adjudication(be, oracle, name, n=2000, what=what)
+    assert not bad, "%s: farther from the binary128 truth than the reference is: %s" % (cfg, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad])
