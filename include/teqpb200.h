@@ -97,7 +97,18 @@ int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long
 int get_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                     const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
 
+/* VirialDerivatives::get_dmBnvirdTm (teqpcpp.hpp:131; derivs.hpp:780-841) for many temperatures: out[k] = d^NT B_Nvir / dT^NT.  Nvir 2..7 for
+   NT = 0, 2..5 for NT = 1, 2 (the scalar reference entry above serves Nvir 2..4); composition rows as in get_Ar0n_batch */
+int get_dmBnvirdTm_batch(const long long int uuid, const int Nvir, const int NT, const long long int npts, const double* T, const double* molefrac,
+                         const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+/* IsochoricDerivatives::get_Psir_sigma_derivs (teqpcpp.hpp:160; derivs.hpp:1496-1509): out[k][p] = d^k Psir(T, rhovec + sigma v) / dsigma^k at
+   sigma = 0, k = 0..4; rhovec and v are [Ncomp][npts] */
+int get_Psir_sigma_derivs_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const double* v,
+                                const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
+
 /* ---------------- utilities ---------------- */
+/* AbstractModel::get_reducing_temperature (which = 0) / get_reducing_density (which = 1), teqpcpp.hpp:124-125: multi-fluid families only */
+int teqpb200_get_reducing(const long long int uuid, const int which, const double* molefrac, const int Ncomp, double* val, char* errmsg, int errmsg_length);
 int teqpb200_get_R(const long long int uuid, const double* molefrac, const int Ncomp, double* R, char* errmsg, int errmsg_length); /* AbstractModel::get_R, teqpcpp.hpp:102 */
 int teqpb200_get_ncomp(const long long int uuid, int* Ncomp, char* errmsg, int errmsg_length);
 int teqpb200_device_count(void);

@@ -60,6 +60,11 @@ std::unique_ptr<AbstractModel> build(const nlohmann::json& j, std::string& kind)
     throw std::invalid_argument("Don't understand \"kind\" of: " + kind);
 }
 
+}  // namespace
+// C++ entry for interop/test_b200_model.cpp: the reference's AbstractModel for a spec (what teqp::cppinterface::make_model returns for it)
+std::unique_ptr<teqp::cppinterface::AbstractModel> teqp_ref_oracle_make_model(const nlohmann::json& j) { std::string kind; return build(j, kind); }
+namespace {
+
 void put_err(const std::string& msg, char* err, int errlen) {
     if (err && errlen > 0) { std::strncpy(err, msg.c_str(), errlen - 1); err[errlen - 1] = 0; }
 }
@@ -307,4 +312,49 @@ int ref_lnphi_family(void* h, int what, long long npts, const double* T, const d
 
 int ref_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 
+
+// AbstractModel::get_dmBnvirdTm (teqpcpp.hpp:131; VirialDerivatives::get_dmBnvirdTm_runtime, derivs.hpp:808-841) per temperature;
+// Nvir > 4 with NT = 0 goes through get_Bnvir (derivs.hpp:715-752)
+int ref_get_dmBnvirdTm(void* h, int Nvir, int NTd, long long npts, const double* T, const double* x, int ncomp, double* out, int nthreads,
+                       char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        if (Nvir > 4 && NTd == 0) out[k] = am.get_Bnvir(Nvir, T[k], z)[Nvir];
+        else out[k] = am.get_dmBnvirdTm(Nvir, NTd, T[k], z);
+    });
+}
+// AbstractModel::get_Psir_sigma_derivs (teqpcpp.hpp:160; derivs.hpp:1496-1509): out[5][npts]
+int ref_Psir_sigma_derivs(void* h, long long npts, const double* T, const double* rhovec, const double* v, int ncomp, double* out, int nthreads,
+                          char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd r, d; if (r.size() != ncomp) { r.resize(ncomp); d.resize(ncomp); }
+        gather(rhovec, npts, k, ncomp, r); gather(v, npts, k, ncomp, d);
+        const Eigen::ArrayXd o = am.get_Psir_sigma_derivs(T[k], r, d);
+        for (int i = 0; i < 5; ++i) out[(long long)i * npts + k] = o[i];
+    });
+}
+// AbstractModel::get_deriv_mat2 (teqpcpp.hpp:164; DerivativeHolderSquare<2>, derivs.hpp:1512-1536): the six entries the reference fills,
+// out[6][npts] = (0,0) (0,1) (0,2) (1,0) (2,0) (1,1)
+int ref_deriv_mat2(void* h, long long npts, const double* T, const double* rho, const double* x, int ncomp, double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        const auto m = am.get_deriv_mat2(T[k], rho[k], z);
+        const double v[6] = {m(0, 0), m(0, 1), m(0, 2), m(1, 0), m(2, 0), m(1, 1)};
+        for (int i = 0; i < 6; ++i) out[(long long)i * npts + k] = v[i];
+    });
+}
+// AbstractModel::get_reducing_temperature / get_reducing_density (teqpcpp.hpp:124-125), one composition
+int ref_get_reducing(void* h, int which, const double* z, int ncomp, double* out, char* err, int errlen) {
+    REF_TRY
+    Eigen::ArrayXd zz = Eigen::Map<const Eigen::ArrayXd>(z, ncomp);
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    *out = which == 0 ? am.get_reducing_temperature(zz) : am.get_reducing_density(zz);
+    return 0;
+    REF_CATCH
+}
 } // extern "C"

@@ -375,8 +375,73 @@ int get_AtaudeltaXiXj(const long long int uuid, const double, const int, const d
                       const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXj"); }
 int get_AtaudeltaXiXjXk(const long long int uuid, const double, const int, const double, const int, const double*, const int,
                         const int, const int, const int, const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXjXk"); }
-int get_dmBnvirdTm(const long long int uuid, const int, const int, const double, const double*, const int, double*, char* errmsg,
-                   int errmsg_length) { TQ_NOT_YET("get_dmBnvirdTm"); }
+// VirialDerivatives::get_dmBnvirdTm_runtime (derivs.hpp:808-841): d^m B_n / dT^m = 1/(n-2)! d^(n-1+m) alphar / dT^m drho^(n-1) at rho = 0.
+// One unit-seeded jet sweep at rho = 0 gives D_k = (1/T)^k d^k/d(1/T)^k of d^(n-1) alphar / drho^(n-1); with u = 1/T:
+//   dB/dT = -D_1 / T,   d2B/dT2 = (D_2 + 2 D_1) / T^2
+static void virial_call(const Model& m, int Nvir, int NTd, long long npts, const double* T, const double* x, int Ncomp, double* out, int flags) {
+    check_ncomp(m, Ncomp);
+    if (Nvir < 2 || Nvir > 7) throw std::invalid_argument("Nderiv is invalid in get_dmBnvirdTm_runtime");
+    if (NTd < 0 || NTd > 3) throw std::invalid_argument("NTderiv is invalid in get_dmBnvirdTm_runtime");
+    if (NTd == 3 || (NTd > 0 && Nvir > 5)) throw NotImplementedError("get_dmBnvirdTm: third temperature derivatives (and T-derivatives of B_6, B_7) need a jet shape libteqpb200 does not compile");
+    const int ND = Nvir - 1;
+    const bool bc = flags & TEQPB200_BROADCAST_X;
+    double fact = 1.0;
+    for (int k = 2; k <= Nvir - 2; ++k) fact *= k;
+    const int rows = (NTd + 1) * (ND + 1);
+    // rho = 0 everywhere: a device scratch row (device-pointer calls) or a host vector (host calls) of zeros
+    std::vector<double> zeros_h;
+    double* zeros_d = nullptr;
+    const double* rho = nullptr;
+    if (flags & TEQPB200_DEVICE_PTRS) {
+        TQ_CUDA(cudaMallocAsync(&zeros_d, sizeof(double) * (size_t)npts, tl_stream));
+        TQ_CUDA(cudaMemsetAsync(zeros_d, 0, sizeof(double) * (size_t)npts, tl_stream));
+        rho = zeros_d;
+    } else { zeros_h.assign((size_t)npts, 0.0); rho = zeros_h.data(); }
+    std::vector<double> tab_h;
+    double* tab = nullptr;
+    if (flags & TEQPB200_DEVICE_PTRS) TQ_CUDA(cudaMallocAsync(&tab, sizeof(double) * (size_t)rows * npts, tl_stream));
+    else { tab_h.resize((size_t)rows * npts); tab = tab_h.data(); }
+    run(flags, npts, {{T, 1, false}, {rho, 1, false}, {x, Ncomp, bc}}, {{tab, rows}},
+        [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+            DeviceBatch b = make_batch(n, din[0], din[1], din[2], bc);
+            b.rho_unit_seed = 1;
+            m.launch_virial_table(NTd, ND, b, dout[0], st);
+            ++g_launches;
+        });
+    if (flags & TEQPB200_DEVICE_PTRS) {
+        // combine on the host for simplicity of this (not hot) path: copy the needed rows down, write the result back
+        std::vector<double> h((size_t)rows * npts), T_h((size_t)npts), o((size_t)npts);
+        TQ_CUDA(cudaMemcpyAsync(h.data(), tab, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, tl_stream));
+        TQ_CUDA(cudaMemcpyAsync(T_h.data(), T, sizeof(double) * (size_t)npts, cudaMemcpyDeviceToHost, tl_stream));
+        TQ_CUDA(cudaStreamSynchronize(tl_stream));
+        for (long long k = 0; k < npts; ++k) {
+            const double D0 = h[(size_t)(0 * (ND + 1) + ND) * npts + k];
+            const double D1 = NTd >= 1 ? h[(size_t)(1 * (ND + 1) + ND) * npts + k] : 0.0, D2 = NTd >= 2 ? h[(size_t)(2 * (ND + 1) + ND) * npts + k] : 0.0;
+            const double Tk = T_h[k];
+            o[k] = (NTd == 0 ? D0 : NTd == 1 ? -D1 / Tk : (D2 + 2.0 * D1) / (Tk * Tk)) / fact;
+        }
+        TQ_CUDA(cudaMemcpyAsync(out, o.data(), sizeof(double) * (size_t)npts, cudaMemcpyHostToDevice, tl_stream));
+        TQ_CUDA(cudaStreamSynchronize(tl_stream));
+        TQ_CUDA(cudaFreeAsync(tab, tl_stream));
+        TQ_CUDA(cudaFreeAsync(zeros_d, tl_stream));
+    } else {
+        for (long long k = 0; k < npts; ++k) {
+            const double D0 = tab[(size_t)(0 * (ND + 1) + ND) * npts + k];
+            const double D1 = NTd >= 1 ? tab[(size_t)(1 * (ND + 1) + ND) * npts + k] : 0.0, D2 = NTd >= 2 ? tab[(size_t)(2 * (ND + 1) + ND) * npts + k] : 0.0;
+            out[k] = (NTd == 0 ? D0 : NTd == 1 ? -D1 / T[k] : (D2 + 2.0 * D1) / (T[k] * T[k])) / fact;
+        }
+    }
+}
+
+int get_dmBnvirdTm(const long long int uuid, const int Nvir, const int NT, const double T, const double* molefrac, const int Ncomp, double* val,
+                   char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        // the reference's runtime dispatch serves B_2..B_4 with 0..3 temperature derivatives (derivs.hpp:808-841)
+        if (Nvir < 2 || Nvir > 4) throw std::invalid_argument("Nderiv is invalid in get_dmBnvirdTm_runtime");
+        virial_call(*m, Nvir, NT, 1, &T, molefrac, Ncomp, val, 0);
+    });
+}
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Part 2: batched
@@ -531,9 +596,37 @@ int get_fugacity_coefficients_batch(const long long int uuid, const long long in
     return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, nullptr, nullptr, nullptr, nullptr, out, flags); });
 }
 
+int get_dmBnvirdTm_batch(const long long int uuid, const int Nvir, const int NT, const long long int npts, const double* T, const double* molefrac,
+                         const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { if (npts > 0) virial_call(*lookup(uuid), Nvir, NT, npts, T, molefrac, Ncomp, out, flags); });
+}
+int get_Psir_sigma_derivs_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const double* v,
+                                const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (flags & TEQPB200_BROADCAST_X) throw InvalidArgument("TEQPB200_BROADCAST_X does not apply to rhovec inputs");
+        run(flags, npts, {{T, 1, false}, {rhovec, Ncomp, false}, {v, Ncomp, false}}, {{out, 5}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                m->launch_sigma_derivs(make_batch(n, din[0], nullptr, din[1], false), din[2], dout[0], st);
+                ++g_launches;
+            });
+    });
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // utilities
 // ---------------------------------------------------------------------------------------------------------------------
+int teqpb200_get_reducing(const long long int uuid, const int which, const double* molefrac, const int Ncomp, double* val, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        double Tr = 0, rhor = 0;
+        // the reference offers these for multi-fluid models only (deriv_adapter.hpp: has_meth_get_reducing_*)
+        if (!m->reducing(molefrac, Ncomp, &Tr, &rhor)) throw NotImplementedError(std::string("reducing functions are not defined for model family ") + m->family());
+        *val = which == 0 ? Tr : rhor;
+    });
+}
 int teqpb200_get_R(const long long int uuid, const double* molefrac, const int Ncomp, double* R, char* errmsg, int errmsg_length) {
     return guarded(false, errmsg, errmsg_length, [&] { auto m = lookup(uuid); check_ncomp(*m, Ncomp); *R = m->R(molefrac, Ncomp); });
 }

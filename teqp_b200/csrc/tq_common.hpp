@@ -46,6 +46,8 @@ struct DeviceBatch {
     const double* x = nullptr;
     long long x_stride = 0;  // distance between component rows
     int x_bcast = 0;         // 1: one composition x[ncomp] for every point (x_stride = 1)
+    int rho_unit_seed = 0;   // 1: the density jet is rho(s) = rho0 + s (UNSCALED derivatives d^m/drho^m, needed at rho0 = 0 for the virial
+                             //    coefficients, derivs.hpp:693-867) instead of rho0 (1 + s); honoured by the generic jet kernels only
 };
 
 // What an isochoric-family launch should write; null pointers are skipped.  rhovec is x*rho formed in-kernel exactly as
@@ -104,6 +106,16 @@ public:
     }
     virtual void launch_isoprops(const DeviceBatch&, const IsoPropsOut&, cudaStream_t) const {
         throw NotImplementedError(std::string("derived isochoric properties are not implemented for model family ") + family());
+    }
+    // virial table (VirialDerivatives, derivs.hpp:693-867): out[(n*(ND+1)+m)][npts] = (1/T)^n d^(n+m) alphar / d(1/T)^n drho^m at the batch's
+    // rho (= 0), i.e. the Lambda table with UNSCALED density derivatives; `in.rho_unit_seed` is set by the caller
+    virtual void launch_virial_table(int, int, const DeviceBatch&, double*, cudaStream_t) const {
+        throw NotImplementedError(std::string("virial coefficients are not implemented for model family ") + family());
+    }
+    // IsochoricDerivatives::get_Psir_sigma_derivs (derivs.hpp:1496-1509): d^k Psir(T, rhovec + sigma v) / dsigma^k, k = 0..4;
+    // in.x = rhovec rows, v[ncomp][npts], out[5][npts]
+    virtual void launch_sigma_derivs(const DeviceBatch&, const double*, double*, cudaStream_t) const {
+        throw NotImplementedError(std::string("get_Psir_sigma_derivs is not implemented for model family ") + family());
     }
     // reducing functions (teqpcpp.hpp get_reducing_density / get_reducing_temperature); host, single composition
     virtual bool reducing(const double*, int, double*, double*) const { return false; }

@@ -18,6 +18,8 @@
 
 namespace tq {
 void cubic_launch_isoprops(const CubicParams&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
+void cubic_launch_virial(const CubicParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);   // tq_ex_cubic.cu
+void cubic_launch_sigma(const CubicParams&, const DeviceBatch&, const double*, double*, cudaStream_t);
 void cubic_launch_ATrhoXiXj(const CubicParams&, const DeviceBatch&, int, int, double*, cudaStream_t);
 void cubic_launch_ATrhoXiXjXk(const CubicParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 
@@ -61,6 +63,8 @@ public:
         }
         TQ_CUDA(cudaGetLastError());
     }
+    void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { cubic_launch_virial(p, NT, ND, in, out, st); }
+    void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { cubic_launch_sigma(p, in, v, out, st); }
     void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override {
         if (NT < 0 || NT > kMaxDerivT || ND < 0 || ND > kMaxDerivD) throw InvalidArgument("derivative order out of range");
         if (in.npts == 0) return;

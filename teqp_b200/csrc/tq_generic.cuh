@@ -28,7 +28,7 @@ template<class M> struct small_variants<M, std::void_t<decltype(M::kNoSmallVaria
 // ------------------------------------------------------------------------------------------------------------------
 template<class M, int MAXN, int CT, int CD>
 TQ_HD void generic_ar_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin,
-                            const int NT, const int ND, double* out, const long long ostride) {
+                            const int NT, const int ND, double* out, const long long ostride, const bool rho_unit_seed = false) {
     using XT = J3<0, 0, 0>;
     XT x[MAXN];
 #pragma unroll(MAXN <= 4 ? MAXN : 1)
@@ -38,7 +38,7 @@ TQ_HD void generic_ar_point(const typename M::Params& p, const int nc, const dou
     using RT = J3<0, CD, 0>;
     const TT T = TT::reciprocal_scaled_variable(T0);
     RT rho;
-    rho.c[0] = Tay<CD, Tay<0, double>>::scaled_variable(rho0);
+    rho.c[0] = rho_unit_seed ? Tay<CD, Tay<0, double>>::unit_variable(rho0) : Tay<CD, Tay<0, double>>::scaled_variable(rho0);
     const J3<CT, CD, 0> a = embed<J3<CT, CD, 0>>(M::template alphar<MAXN>(p, T, rho, x));
     double fn = 1.0;
 #pragma unroll
@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(128) generic_ar_table_kernel(const __grid_cons
     for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
         double x[MAXN];
         load_x<M, MAXN>(x, nc, in, k);
-        generic_ar_point<M, MAXN, CT, CD>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, NT, ND, out + k, npts);
+        generic_ar_point<M, MAXN, CT, CD>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, NT, ND, out + k, npts, in.rho_unit_seed != 0);
     }
 }
 
@@ -504,6 +504,53 @@ void generic_launch_isoprops(const typename M::Params& p, int nc, const DeviceBa
     if (in.npts == 0) return;
     const int block = 64;
     generic_isoprops_kernel<M><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, o);
+    TQ_CUDA(cudaGetLastError());
+}
+#endif  // __CUDACC__
+
+
+// ------------------------------------------------------------------------------------------------------------------
+// get_Psir_sigma_derivs (derivs.hpp:1496-1509): Psi^r(T, rhovec + sigma v) to fourth order in sigma, one Tay<4> sweep
+// (the reference uses autodiff::Real<4> the same way): out[k][npts] = d^k Psir / dsigma^k, k = 0..4
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN>
+TQ_HD void generic_sigma_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const double* v, double* out,
+                               const long long ostride) {
+    const J3<0, 0, 4> a = psir_dir_jet<M, MAXN, 0, 0, 4>(p, nc, T0, rv, -1, v);
+    double f = 1.0;
+#pragma unroll
+    for (int k = 0; k <= 4; ++k) {
+        if (k >= 2) f *= double(k);
+        out[(long long)k * ostride] = f * a.c[0].c[0].c[k];
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int MAXN>
+__global__ void __launch_bounds__(64) generic_sigma_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                           const double* __restrict__ vdir, double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double rv[MAXN], v[MAXN];
+#pragma unroll(MAXN <= 4 ? MAXN : 1)
+        for (int i = 0; i < MAXN; ++i)
+            if (i < nc) { rv[i] = __ldg(in.x + (long long)i * in.x_stride + k); v[i] = __ldg(vdir + (long long)i * npts + k); }
+        generic_sigma_point<M, MAXN>(p, nc, __ldg(in.T + k), rv, v, out + k, npts);
+    }
+}
+
+template<class M>
+void generic_launch_sigma(const typename M::Params& p, int nc, const DeviceBatch& in, const double* v, double* out, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    const int grid = grid_for(in.npts, block, sm_count() * 32);
+    if constexpr (small_variants<M>::value) {
+        if (nc <= 2) generic_sigma_kernel<M, 2><<<grid, block, 0, st>>>(p, nc, in, v, out);
+        else generic_sigma_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, v, out);
+    } else {
+        generic_sigma_kernel<M, M::kMaxC><<<grid, block, 0, st>>>(p, nc, in, v, out);
+    }
     TQ_CUDA(cudaGetLastError());
 }
 #endif  // __CUDACC__

@@ -19,6 +19,8 @@ namespace tq {
 void gergjet_launch_isoprops(const GergProgram&, const DeviceBatch&, const IsoPropsOut&, cudaStream_t);
 void gergjet_launch_ATrhoXiXj(const GergProgram&, const DeviceBatch&, int, int, double*, cudaStream_t);
 void gergjet_launch_ATrhoXiXjXk(const GergProgram&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
+void gergjet_launch_virial(const GergProgram&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);   // tq_ex_gergjet.cu
+void gergjet_launch_sigma(const GergProgram&, const DeviceBatch&, const double*, double*, cudaStream_t);
 
 namespace {
 
@@ -103,6 +105,26 @@ public:
     void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXj(P, in, i, j, out, st); }
     void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXjXk(P, in, i, j, k, out, st); }
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { gergjet_launch_isoprops(P, in, o, st); }
+    // GERG200XReducing::get_Tr / get_rhor (GERG.hpp:179-205) on the host, same pair order and skip rule as the kernels
+    bool reducing(const double* x, int n, double* Tr, double* rhor) const override {
+        if (n != P.nc) throw InvalidArgument("mole fractions must be of size " + std::to_string(P.nc));
+        double YT = 0, YV = 0;
+        int q = 0;
+        for (int i = 0; i < P.nc; ++i) {
+            YT += x[i] * x[i] * P.Tc[i]; YV += x[i] * x[i] * P.vc[i];
+            for (int j = i + 1; j < P.nc; ++j, ++q) {
+                const GergRedPair& pr = P.pair[q];
+                const double dT = pr.beta2T * x[i] + x[j], dV = pr.beta2V * x[i] + x[j];
+                if (dT == 0.0 || dV == 0.0) continue;
+                const double num = x[i] * x[j] * (x[i] + x[j]);
+                YT += num / dT * pr.YT2; YV += num / dV * pr.YV2;
+            }
+        }
+        *Tr = YT; *rhor = 1.0 / YV;
+        return true;
+    }
+    void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { gergjet_launch_virial(P, NT, ND, in, out, st); }
+    void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { gergjet_launch_sigma(P, in, v, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         gerg_launch_isochoric(P, Rgas, in, o, st);
     }

@@ -20,6 +20,7 @@ void gsaft_launch_ar_rho(const GsaftParams&, int ND, const DeviceBatch&, double*
 void gsaft_launch_ar_mixed(const GsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_ATrhoXi(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_isochoric(const GsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void gsaft_launch_sigma(const GsaftParams&, const DeviceBatch&, const double*, double*, cudaStream_t);   // tq_ex_gsaft.cu
 
 namespace {
 
@@ -53,6 +54,8 @@ public:
         if (NT == 0) gsaft_launch_ar_rho(p, ND, in, out, st);
         else gsaft_launch_ar_mixed(p, NT, ND, in, out, st);
     }
+    void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { launch_ar_table(NT, ND, in, out, st); }
+    void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { gsaft_launch_sigma(p, in, v, out, st); }
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gsaft_launch_ATrhoXi(p, in, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { gsaft_launch_isochoric(p, in, o, st); }
 };

@@ -14,6 +14,7 @@ void pcsaft_launch_ar_rho(const PcsaftParams&, int ND, const DeviceBatch&, doubl
 void pcsaft_launch_ar_mixed(const PcsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
 void pcsaft_launch_ATrhoXi(const PcsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void pcsaft_launch_isochoric(const PcsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void pcsaft_launch_sigma(const PcsaftParams&, const DeviceBatch&, const double*, double*, cudaStream_t);   // tq_ex_pcsaft.cu
 
 namespace {
 
@@ -60,6 +61,8 @@ public:
         if (NT == 0) pcsaft_launch_ar_rho(p, ND, in, out, st);
         else pcsaft_launch_ar_mixed(p, NT, ND, in, out, st);
     }
+    void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { launch_ar_table(NT, ND, in, out, st); }
+    void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { pcsaft_launch_sigma(p, in, v, out, st); }
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { pcsaft_launch_ATrhoXi(p, in, out, st); }
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { pcsaft_launch_isoprops(p, in, o, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { pcsaft_launch_isochoric(p, in, o, st); }

@@ -173,6 +173,67 @@ class Model:
     def get_fugacity_coefficients_batch(self, T, rhovec, out=None):
         return self._iso(lib().get_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]], out)[0]
 
+    def get_dmBnvirdTm_batch(self, Nvir, NT, T, x, out=None):
+        """d^NT B_Nvir / dT^NT for an array of temperatures (VirialDerivatives::get_dmBnvirdTm, derivs.hpp:780-841); x: [Ncomp][npts] or [Ncomp]"""
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        if len(tuple(x.shape)) == 1:
+            flags |= BROADCAST_X
+        aT, ax = _Arg(T, dev), _Arg(x, dev)
+        ao = _Arg(self._out((n,), dev, T, out), dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_dmBnvirdTm_batch(self._uuid, C.c_int(Nvir), C.c_int(NT), C.c_longlong(n), aT.ptr, ax.ptr, C.c_int(x.shape[0]), ao.ptr,
+                                          C.c_int(flags), err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_Psir_sigma_derivs_batch(self, T, rhovec, v, out=None):
+        """[5][npts]: d^k Psir(T, rhovec + sigma v)/dsigma^k, k = 0..4 (IsochoricDerivatives::get_Psir_sigma_derivs, derivs.hpp:1496-1509)"""
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        aT, ar, av = _Arg(T, dev), _Arg(rhovec, dev), _Arg(v, dev)
+        ao = _Arg(self._out((5, n), dev, T, out), dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().get_Psir_sigma_derivs_batch(self._uuid, C.c_longlong(n), aT.ptr, ar.ptr, av.ptr, C.c_int(rhovec.shape[0]), ao.ptr, C.c_int(flags),
+                                                 err, C.c_int(2000)), err)
+        return ao.obj
+
+    def get_reducing_temperature(self, molefrac):
+        return self._reducing(0, molefrac)
+
+    def get_reducing_density(self, molefrac):
+        return self._reducing(1, molefrac)
+
+    def _reducing(self, which, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().teqpb200_get_reducing(self._uuid, C.c_int(which), z.ctypes.data_as(_dp), C.c_int(z.size), C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_dmBnvirdTm(self, Nvir, NT, T, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(lib().get_dmBnvirdTm(self._uuid, C.c_int(Nvir), C.c_int(NT), C.c_double(T), z.ctypes.data_as(_dp), C.c_int(z.size), C.byref(out), err,
+                                    C.c_int(2000)), err)
+        return out.value
+
+    def get_B2vir(self, T, molefrac):
+        return self.get_dmBnvirdTm(2, 0, T, molefrac)
+
+    def get_Psir_sigma_derivs(self, T, rhovec, v):
+        r = np.ascontiguousarray(rhovec, dtype=np.float64).reshape(-1, 1); d = np.ascontiguousarray(v, dtype=np.float64).reshape(-1, 1)
+        return self.get_Psir_sigma_derivs_batch(np.array([float(T)]), r, d)[:, 0]
+
+    def get_deriv_mat2(self, T, rho, molefrac):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        pairs = [(i, j) for i in range(3) for j in range(3)]
+        return self.get_Arxy_batch(pairs, np.array([float(T)]), np.array([float(rho)]), z.reshape(-1, 1))[:, 0].reshape(3, 3)
+
     # ------------------------------------------------------------------ reference scalar surface
     def get_R(self, molefrac):
         z = np.ascontiguousarray(molefrac, dtype=np.float64)

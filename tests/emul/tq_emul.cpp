@@ -56,6 +56,30 @@ void generic_loop(const typename M::Params& p, int nc, int NT, int ND, long long
         generic_ar_point<M, M::kMaxC, CT, CD>(p, nc, T[k], rho[k], xx, NT, ND, out + k, npts);
     }
 }
+// virial tables: unit-seeded density jet at rho = 0 (what launch_virial_table runs), T-major [NT+1][ND+1]
+template<class M, int CT, int CD>
+void virial_loop(const typename M::Params& p, int nc, int NT, int ND, long long npts, const double* T, const double* x, long long xs, double* out) {
+    for (long long k = 0; k < npts; ++k) {
+        double xx[M::kMaxC];
+        for (int i = 0; i < nc; ++i) xx[i] = x[(long long)i * xs + (xs ? k : 0)];
+        generic_ar_point<M, M::kMaxC, CT, CD>(p, nc, T[k], 0.0, xx, NT, ND, out + k, npts, true);
+    }
+}
+template<class M>
+void virial_table(const typename M::Params& p, int nc, int NT, int ND, long long npts, const double* T, const double* x, long long xs, double* out) {
+    if (NT == 0 && ND <= 4) virial_loop<M, 0, 4>(p, nc, NT, ND, npts, T, x, xs, out);
+    else if (NT == 0) virial_loop<M, 0, 6>(p, nc, NT, ND, npts, T, x, xs, out);
+    else if (NT <= 2 && ND <= 4) virial_loop<M, 2, 4>(p, nc, NT, ND, npts, T, x, xs, out);
+    else throw InvalidArgument("shape not compiled in the emulation harness");
+}
+template<class M>
+void sigma_loop(const typename M::Params& p, int nc, long long npts, const double* T, const double* rv, const double* v, double* out) {
+    for (long long k = 0; k < npts; ++k) {
+        double r[M::kMaxC], d[M::kMaxC];
+        for (int i = 0; i < nc; ++i) { r[i] = rv[(long long)i * npts + k]; d[i] = v[(long long)i * npts + k]; }
+        generic_sigma_point<M, M::kMaxC>(p, nc, T[k], r, d, out + k, npts);
+    }
+}
 template<class M>
 void generic_table(const typename M::Params& p, int nc, int NT, int ND, long long npts, const double* T, const double* rho, const double* x, long long xs, double* out) {
     if (NT == 0 && ND <= 4) generic_loop<M, 0, 4>(p, nc, NT, ND, npts, T, rho, x, xs, out);
@@ -148,6 +172,27 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             generic_table<GsaftDev>(p, p.mie.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
         }
+        throw InvalidArgument("family not wired in the emulation harness: " + fam);
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+// what = 0: virial table [NT+1][ND+1][npts] at rho = 0 (x broadcast if broadcast != 0);  what = 1: sigma derivatives out[5][npts] (x = rhovec, v)
+int emul_extras(const char* json, int what, int NT, int ND, long long npts, const double* T, const double* x, const double* v, int ncomp, int broadcast,
+                double* out, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        size_t nb = 0;
+        const void* blob = m->params_blob(&nb);
+        const std::string fam = m->family();
+        const long long xs = broadcast ? 0 : npts;
+#define TQ_FAM(M, P, NC) { const typename M::Params& p = *static_cast<const typename M::Params*>(blob); \
+            if (what == 0) virial_table<M>(p, NC, NT, ND, npts, T, x, xs, out); else sigma_loop<M>(p, NC, npts, T, x, v, out); return 0; }
+        if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") TQ_FAM(GergJetDev, GergProgram, p.nc)
+        if (fam == "cubic" || fam == "vdW") TQ_FAM(CubicDev, CubicParams, p.nc)
+        if (fam == "PCSAFT") TQ_FAM(PcsaftDev, PcsaftParams, p.nc)
+        if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") TQ_FAM(GsaftDev, GsaftParams, p.mie.nc)
+#undef TQ_FAM
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
 }

@@ -101,6 +101,41 @@ def isochoric(spec, T, rhovec, hess=True):
 _JIT_CACHE = {}
 
 
+def virial_table(spec, NT, ND, T, x):
+    """[NT+1][ND+1][n]: (1/T)^n d^(n+m) alphar / d(1/T)^n drho^m at rho = 0 (unit-seeded density jet)"""
+    T = np.ascontiguousarray(T, dtype=np.float64); x = np.ascontiguousarray(x, dtype=np.float64)
+    n = T.size; bc = x.ndim == 1
+    out = np.empty(((NT + 1) * (ND + 1), n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_extras(json.dumps(spec).encode(), C.c_int(0), C.c_int(NT), C.c_int(ND), C.c_longlong(n), _p(T), _p(x), None, C.c_int(x.shape[0]),
+                           C.c_int(1 if bc else 0), _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out.reshape(NT + 1, ND + 1, n)
+
+
+def dmBnvirdTm(spec, Nvir, NT, T, x):
+    """the combination libteqpb200's virial_call forms from the table (csrc/tq_capi.cu)"""
+    import math
+    tab = virial_table(spec, NT, Nvir - 1, T, x)
+    D = tab[:, Nvir - 1]
+    f = math.factorial(Nvir - 2)
+    T = np.asarray(T, dtype=np.float64)
+    return (D[0] if NT == 0 else -D[1] / T if NT == 1 else (D[2] + 2 * D[1]) / T**2) / f
+
+
+def sigma_derivs(spec, T, rv, v):
+    T = np.ascontiguousarray(T, dtype=np.float64); rv = np.ascontiguousarray(rv, dtype=np.float64); v = np.ascontiguousarray(v, dtype=np.float64)
+    n = T.size
+    out = np.empty((5, n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_extras(json.dumps(spec).encode(), C.c_int(1), C.c_int(0), C.c_int(0), C.c_longlong(n), _p(T), _p(rv), _p(v), C.c_int(rv.shape[0]),
+                           C.c_int(0), _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out
+
+
 def jit_ar_table(spec, NT, ND, T, rho, x):
     import hashlib
     import subprocess

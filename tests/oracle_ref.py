@@ -144,6 +144,39 @@ class RefModel:
         self._call(lib().ref_Psir_fgradHessian, C.c_int(0), C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), _p(f), _p(g), _p(H))
         return f, g, H
 
+    def dmBnvirdTm(self, Nvir, NT, T, x):
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        n = T.size
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        if x.ndim == 1:
+            x = np.ascontiguousarray(np.tile(x[:, None], (1, n)))
+        out = np.empty(n)
+        self._call(lib().ref_get_dmBnvirdTm, C.c_int(Nvir), C.c_int(NT), C.c_longlong(n), _p(T), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
+    def sigma_derivs(self, T, rhovec, v):
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        n = T.size; rv = _soa(rhovec, n); vv = _soa(v, n)
+        out = np.empty((5, n))
+        self._call(lib().ref_Psir_sigma_derivs, C.c_longlong(n), _p(T), _p(rv), _p(vv), C.c_int(rv.shape[0]), _p(out))
+        return out
+
+    def deriv_mat2(self, T, rho, x):
+        T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
+        n = T.size; x = _soa(x, n)
+        out = np.empty((6, n))
+        self._call(lib().ref_deriv_mat2, C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
+    def reducing(self, which, z):
+        z = np.ascontiguousarray(z, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        rc = lib().ref_get_reducing(C.c_void_p(self.h), C.c_int(which), _p(z), C.c_int(len(z)), C.byref(out), err, C.c_int(2000))
+        if rc != 0:
+            raise RuntimeError(err.value.decode())
+        return out.value
+
     def lnphi_family(self, what, T, rhovec):
         T = np.ascontiguousarray(T, dtype=np.float64)
         n = T.size; rv = _soa(rhovec, n); nc = rv.shape[0]

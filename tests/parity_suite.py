@@ -35,6 +35,12 @@ class EmulBackend:
     def isoprops(self, spec, T, rv):
         return self.e.isoprops(spec, T, rv)
 
+    def dmBnvirdTm(self, spec, Nvir, NT, T, x):
+        return self.e.dmBnvirdTm(spec, Nvir, NT, T, x)
+
+    def sigma_derivs(self, spec, T, rv, v):
+        return self.e.sigma_derivs(spec, T, rv, v)
+
     def isochoric(self, spec, T, rv):
         f, g, H, lnphi, phi = self.e.isochoric(spec, T, rv)
         nc = rv.shape[0]
@@ -74,6 +80,12 @@ class GpuBackend:
 
     def isoprops(self, spec, T, rv):
         return self.model(spec).isochoric_properties_batch(T, rv)
+
+    def dmBnvirdTm(self, spec, Nvir, NT, T, x):
+        return self.model(spec).get_dmBnvirdTm_batch(Nvir, NT, T, x)
+
+    def sigma_derivs(self, spec, T, rv, v):
+        return self.model(spec).get_Psir_sigma_derivs_batch(T, rv, v)
 
     def isochoric(self, spec, T, rv):
         m = self.model(spec)
@@ -349,3 +361,36 @@ def truth_adjudication(be, oracle, name, n=2000, what=("ar", "atrhoxi", "iso")):
     k = ADJ_FACTOR.get(name, 2.0)
     bad = [r for r in rows if r["gpu_vs_truth_max"] > k * r["oracle_vs_truth_max"] + 4 * EPS or r["gpu_vs_truth_p999"] > k * r["oracle_vs_truth_p999"] + 4 * EPS]
     return rows, bad
+
+
+def virials(be, oracle, name, n=200):
+    """VirialDerivatives (derivs.hpp:693-867): B_2..B_4 and their first two temperature derivatives, B_5..B_7 (get_Bnvir), against the
+    reference's AbstractModel::get_dmBnvirdTm / get_Bnvir.  Floor scale: |T^k d^k B_n / dT^k| / T^NT over k <= NT (same jet)."""
+    spec, T, rho, x = cases.points(name, n)
+    m = oracle.RefModel(spec)
+    # rho = 0 is where the SAFT families' association / hard-sphere expressions are worst conditioned in BOTH implementations
+    rt = 1e-10 if name.startswith(("MIE", "GSAFT")) else 1e-12
+    for Nvir in (2, 3, 4):
+        ref = [m.dmBnvirdTm(Nvir, k, T, x) for k in range(3)]
+        for NT in range(3):
+            got = be.dmBnvirdTm(spec, Nvir, NT, T, x)
+            S = np.max([np.abs(ref[k]) * T**k for k in range(NT + 1)], axis=0) / T**NT
+            parity.check("%s d^%d B_%d/dT^%d" % (name, NT, Nvir, NT), got, ref[NT], S, rtol=rt, ftol=10 * parity.FTOL)
+    for Nvir in (5, 6, 7):
+        ref5 = m.dmBnvirdTm(Nvir, 0, T, x)
+        parity.check("%s B_%d" % (name, Nvir), be.dmBnvirdTm(spec, Nvir, 0, T, x), ref5, np.abs(ref5), rtol=1e3 * rt, ftol=0.0)
+
+
+def sigma_derivs(be, oracle, name, n=200):
+    """IsochoricDerivatives::get_Psir_sigma_derivs (derivs.hpp:1496-1509), direction v = a fixed perturbation pattern of rhovec"""
+    spec, T, rho, x = cases.points(name, n)
+    rv = np.ascontiguousarray(x * rho)
+    nc = rv.shape[0]
+    v = np.ascontiguousarray(rv * (1.0 + 0.5 * np.cos(np.arange(nc))[:, None]))   # O(rhovec)-sized direction, not parallel to rhovec
+    m = oracle.RefModel(spec)
+    ref = m.sigma_derivs(T, rv, v)
+    got = be.sigma_derivs(spec, T, rv, v)
+    fam = np.max(np.abs(ref) / np.array([1.0, 1.0, 2.0, 6.0, 24.0])[:, None], axis=0)
+    fam = np.maximum(fam, extra_scale(name) * m.get_R(x[:, 0]) * T * rho)
+    for k in range(5):
+        parity.check("%s Psir_sigma[%d]" % (name, k), got[k], ref[k], fam * parity.fact(k), ftol=5 * parity.FTOL)

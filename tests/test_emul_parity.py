@@ -49,3 +49,13 @@ def test_truth_adjudication(emul, oracle, cfg, name, what):
     percentile of every output of the five BASELINE configs (k = 2; 3 for the SAFT-VR-Mie + association family)"""
     rows, bad = ps.truth_adjudication(ps.EmulBackend(emul), oracle, name, n=300, what=what)
     assert not bad, "%s: farther from the binary128 truth than the reference is: %s" % (cfg, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad])
+
+
+@pytest.mark.parametrize("name", ["PR1", "PR2k", "SRK3", "vdW2", "PCSAFT1", "PCSAFT2", "GERG10", "GERG2004_3", "MIE1", "MIE3", "GSAFT_CR1"])
+def test_virials(emul, oracle, name):
+    ps.virials(ps.EmulBackend(emul), oracle, name, n=200)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG10", "MIE3", "GSAFT_CR1"])
+def test_sigma_derivs(emul, oracle, name):
+    ps.sigma_derivs(ps.EmulBackend(emul), oracle, name, n=200)

@@ -213,3 +213,27 @@ def test_truth_adjudication(be, oracle, cfg, name, what):
     percentile of every output of the five BASELINE configs (k = 2; 3 for the SAFT-VR-Mie + association family)"""
     rows, bad = ps.truth_adjudication(be, oracle, name, n=2000, what=what)
     assert not bad, "%s: farther from the binary128 truth than the reference is: %s" % (cfg, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad])
+
+
+@pytest.mark.parametrize("name", ["PR1", "PR2k", "SRK3", "vdW2", "PCSAFT1", "PCSAFT2", "GERG10", "GERG2004_3", "MIE1", "MIE3", "GSAFT_CR1"])
+def test_virials(be, oracle, name):
+    ps.virials(be, oracle, name, n=200)
+
+
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG10", "MIE3", "GSAFT_CR1"])
+def test_sigma_derivs(be, oracle, name):
+    ps.sigma_derivs(be, oracle, name, n=200)
+
+
+def test_cpp_abstractmodel_adapter():
+    """the C++ side of the boundary: interop/b200_model.cpp (B200Model : teqp::cppinterface::AbstractModel over the C ABI) registered as a
+    plug-in and compared, virtual by virtual, with the reference's own adapter in C++ (interop/test_b200_model.cpp, built by interop/Makefile
+    where /root/reference exists)"""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "interop", "_build", "test_b200_model")
+    if not os.path.exists(exe):
+        pytest.skip("interop/_build/test_b200_model is not built (make -C interop; needs the reference's headers)")
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    print(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:]
