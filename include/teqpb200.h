@@ -97,6 +97,10 @@ int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long
 int get_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                     const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
 
+/* every get_AtaudeltaXi combination in one call (derivs.hpp:341-351; models with alphar_taudelta only, i.e. kind "multifluid"): layout of
+   get_ATrhoXi_table_batch with tau^NT delta^ND d^(NT+ND+NXi) alphar / dtau^NT ddelta^ND dx_i^NXi; host pointers */
+int get_AtaudeltaXi_table_batch(const long long int uuid, const long long int npts, const double* tau, const double* delta, const double* molefrac,
+                                const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
 /* VirialDerivatives::get_dmBnvirdTm (teqpcpp.hpp:131; derivs.hpp:780-841) for many temperatures: out[k] = d^NT B_Nvir / dT^NT.  Nvir 2..7 for
    NT = 0, 2..5 for NT = 1, 2 (the scalar reference entry above serves Nvir 2..4); composition rows as in get_Ar0n_batch */
 int get_dmBnvirdTm_batch(const long long int uuid, const int Nvir, const int NT, const long long int npts, const double* T, const double* molefrac,

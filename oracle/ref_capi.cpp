@@ -17,6 +17,7 @@
 #include "teqp/models/cubics/simple_cubics.hpp"
 #include "teqp/models/GERG/GERG.hpp"
 #include "teqp/models/pcsaft.hpp"
+#include "teqp/models/multifluid.hpp"
 
 #include <thread>
 #include <vector>
@@ -31,6 +32,7 @@ namespace teqp { namespace cppinterface {
     std::unique_ptr<AbstractModel> make_genericSAFT(const nlohmann::json &);
     std::unique_ptr<AbstractModel> make_GERG2004resid(const nlohmann::json &);
     std::unique_ptr<AbstractModel> make_GERG2008resid(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_multifluid(const nlohmann::json &);   // interface/CPP/model_factory_multifluid.cpp
 }}
 
 using namespace teqp;
@@ -57,6 +59,7 @@ std::unique_ptr<AbstractModel> build(const nlohmann::json& j, std::string& kind)
     if (kind == "genericSAFT") return make_genericSAFT(spec);
     if (kind == "GERG2004resid") return make_GERG2004resid(spec);
     if (kind == "GERG2008resid") return make_GERG2008resid(spec);
+    if (kind == "multifluid") return make_multifluid(spec);
     throw std::invalid_argument("Don't understand \"kind\" of: " + kind);
 }
 
@@ -300,6 +303,7 @@ int ref_lnphi_family(void* h, int what, long long npts, const double* T, const d
     else if (rm->kind == "GERG2004resid") { const auto& m = get_model_cref<GERG2004::GERG2004ResidualModel>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "PR" || rm->kind == "SRK" || rm->kind == "cubic") { using M = decltype(make_canonicalPR(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "PCSAFT") { using M = decltype(PCSAFT::PCSAFTfactory(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "multifluid") { using M = decltype(multifluidfactory(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else { put_err("ln(phi) family: kind not wired in the oracle: " + rm->kind, err, errlen); return 200; }
     return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
         thread_local Eigen::ArrayXd r, v; if (r.size() != ncomp) r.resize(ncomp);
@@ -356,5 +360,17 @@ int ref_get_reducing(void* h, int which, const double* z, int ncomp, double* out
     *out = which == 0 ? am.get_reducing_temperature(zz) : am.get_reducing_density(zz);
     return 0;
     REF_CATCH
+}
+// AbstractModel::get_AtaudeltaXi / XiXj / XiXjXk (teqpcpp.hpp:139-141; derivs.hpp:341-414); idx/N hold (i, NXi[, j, NXj[, k, NXk]])
+int ref_get_Ataudelta(void* h, int which, int Ntau, int Ndelta, const int* idx, long long npts, const double* tau, const double* delta, const double* x,
+                      int ncomp, double* out, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        thread_local Eigen::ArrayXd z; if (z.size() != ncomp) z.resize(ncomp);
+        gather(x, npts, k, ncomp, z);
+        if (which == 1) out[k] = am.get_AtaudeltaXi(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1]);
+        else if (which == 2) out[k] = am.get_AtaudeltaXiXj(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1], idx[2], idx[3]);
+        else out[k] = am.get_AtaudeltaXiXjXk(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1], idx[2], idx[3], idx[4], idx[5]);
+    });
 }
 } // extern "C"

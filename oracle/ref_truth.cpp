@@ -20,6 +20,7 @@
 #include "teqp/models/pcsaft.hpp"
 #include "teqp/models/saftvrmie.hpp"
 #include "teqp/models/saft/genericsaft.hpp"
+#include "teqp/models/multifluid.hpp"
 
 #include <atomic>
 #include <cstring>
@@ -44,8 +45,9 @@ using CubicModel = decltype(make_generalizedcubic(nlohmann::json{}));
 using PCSAFTModel = decltype(PCSAFT::PCSAFTfactory(nlohmann::json{}));
 using MieModel = decltype(SAFTVRMie::SAFTVRMiefactory(nlohmann::json{}));
 using GSAFTModel = saft::genericsaft::GenericSAFT;
+using MFModel = decltype(multifluidfactory(nlohmann::json{}));
 using AnyModel = std::variant<vdWEOS1, vdWEOS<double>, PRModel, PCSAFTModel, MieModel, GSAFTModel, GERG2004::GERG2004ResidualModel,
-                              GERG2008::GERG2008ResidualModel>;
+                              GERG2008::GERG2008ResidualModel, MFModel>;
 
 struct TruthModel { std::unique_ptr<AnyModel> m; };
 
@@ -62,6 +64,7 @@ std::unique_ptr<AnyModel> build(const nlohmann::json& j) {
     if (kind == "genericSAFT") return std::make_unique<AnyModel>(GSAFTModel(spec));
     if (kind == "GERG2004resid") return std::make_unique<AnyModel>(GERG2004::GERG2004ResidualModel(spec.at("names").get<std::vector<std::string>>()));
     if (kind == "GERG2008resid") return std::make_unique<AnyModel>(GERG2008::GERG2008ResidualModel(spec.at("names").get<std::vector<std::string>>()));
+    if (kind == "multifluid") return std::make_unique<AnyModel>(multifluidfactory(spec));
     throw std::invalid_argument("truth oracle: don't understand \"kind\" of: " + kind);
 }
 

@@ -7,7 +7,13 @@
 #include <Eigen/Core>
 namespace boost { namespace multiprecision {
 template<unsigned Digits> struct cpp_bin_float {};
+#if defined(SHIM_EP_DOUBLE)
+// (the multifluid term container's std::visit needs one return type for every alternative; GenericCubicTerm / PCSAFTGrossSadowski2001Term
+// return double for a long double density, so that TU maps the stand-in onto double)
+template<typename Backend> using number = double;
+#else
 template<typename Backend> using number = long double;
+#endif
 }}
 namespace Eigen {
 template<typename Op> struct ScalarBinaryOpTraits<double, long double, Op> { typedef long double ReturnType; };

@@ -35,6 +35,7 @@ std::unique_ptr<Model> make_model(const Json& j) {
     if (kind == "PCSAFT") return make_pcsaft_model(spec);
     if (kind == "SAFT-VR-Mie") return make_saftvrmie_model(spec);
     if (kind == "genericSAFT") return make_genericsaft_model(spec);
+    if (kind == "multifluid") return make_multifluid_model(spec);
     throw InvalidArgument("Don't understand \"kind\" of: " + kind);
 }
 
@@ -369,12 +370,62 @@ int get_ATrhoXiXjXk(const long long int uuid, const double T, const int NT, cons
         *val = table[(((NT * 2 + ND) * 2 + NXi) * 2 + NXj) * 2 + NXk];
     });
 }
-int get_AtaudeltaXi(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
-                    const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXi"); }
-int get_AtaudeltaXiXj(const long long int uuid, const double, const int, const double, const int, const double*, const int, const int,
-                      const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXj"); }
-int get_AtaudeltaXiXjXk(const long long int uuid, const double, const int, const double, const int, const double*, const int,
-                        const int, const int, const int, const int, const int, const int, double*, char* errmsg, int errmsg_length) { TQ_NOT_YET("get_AtaudeltaXiXjXk"); }
+// get_AtaudeltaXi / XiXj / XiXjXk (teqpc.h:14-18; derivs.hpp:341-414): as the three calls above with (tau, delta) given instead of (T, rho).
+// Only models with alphar_taudelta (the JSON-driven multifluid kind) serve them; for the others the reference throws as well (derivs.hpp:137-140).
+// The kernels are the same composition-derivative sweeps, driven with T := 1/tau and rho := delta (GergTauDeltaDev, tq_gerg_jet.cuh).
+static void ataudelta_table(const Model& m, int which, int i, int j, int k, long long npts, const double* tau, const double* delta, const double* x,
+                            int Ncomp, int rows, double* out, int flags) {
+    check_ncomp(m, Ncomp);
+    if (flags & TEQPB200_DEVICE_PTRS) throw NotImplementedError("get_Ataudelta tables take host pointers");
+    const bool bc = flags & TEQPB200_BROADCAST_X;
+    std::vector<double> Tinv((size_t)npts);
+    for (long long q = 0; q < npts; ++q) Tinv[q] = 1.0 / tau[q];
+    run(flags, npts, {{Tinv.data(), 1, false}, {delta, 1, false}, {x, Ncomp, bc}}, {{out, rows}},
+        [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+            m.launch_Ataudelta_table(which, make_batch(n, din[0], din[1], din[2], bc), i, j, k, dout[0], st);
+            ++g_launches;
+        });
+}
+int get_AtaudeltaXi(const long long int uuid, const double tau, const int NT, const double delta, const int ND, const double* molefrac, const int Ncomp,
+                    const int i, const int NXi, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (!(NT >= 0 && ND >= 0 && NT + ND <= 2 && NXi >= 0 && NXi <= 3)) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp) throw std::invalid_argument("component index out of range");
+        std::vector<double> table((size_t)Ncomp * 36);
+        ataudelta_table(*m, 1, 0, 0, 0, 1, &tau, &delta, molefrac, Ncomp, Ncomp * 36, table.data(), 0);
+        *val = table[((i * 3 + NT) * 3 + ND) * 4 + NXi];
+    });
+}
+int get_AtaudeltaXiXj(const long long int uuid, const double tau, const int NT, const double delta, const int ND, const double* molefrac, const int Ncomp,
+                      const int i, const int NXi, const int j, const int NXj, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j) throw std::invalid_argument("i cannot equal j");
+        const bool ok = NT >= 0 && ND >= 0 && NT + ND <= 1 && NXi >= 0 && NXj >= 0 && NXi + NXj >= 1 && NXi + NXj <= 2;
+        if (!ok) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp) throw std::invalid_argument("component index out of range");
+        double table[36];
+        ataudelta_table(*m, 2, i, j, 0, 1, &tau, &delta, molefrac, Ncomp, 36, table, 0);
+        *val = table[((NT * 2 + ND) * 3 + NXi) * 3 + NXj];
+    });
+}
+int get_AtaudeltaXiXjXk(const long long int uuid, const double tau, const int NT, const double delta, const int ND, const double* molefrac, const int Ncomp,
+                        const int i, const int NXi, const int j, const int NXj, const int k, const int NXk, double* val, char* errmsg, int errmsg_length) {
+    return guarded(true, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (i == j || j == k || i == k) throw std::invalid_argument("i, j, and k must all be unique");
+        const bool ok = NT >= 0 && ND >= 0 && NT + ND <= 1 && NXi >= 0 && NXi <= 1 && NXj >= 0 && NXj <= 1 && NXk >= 0 && NXk <= 1 && NXi + NXj + NXk >= 2;
+        if (!ok) throw std::invalid_argument("Can't match these derivative counts");
+        if (i < 0 || i >= Ncomp || j < 0 || j >= Ncomp || k < 0 || k >= Ncomp) throw std::invalid_argument("component index out of range");
+        double table[32];
+        ataudelta_table(*m, 3, i, j, k, 1, &tau, &delta, molefrac, Ncomp, 32, table, 0);
+        *val = table[(((NT * 2 + ND) * 2 + NXi) * 2 + NXj) * 2 + NXk];
+    });
+}
 // VirialDerivatives::get_dmBnvirdTm_runtime (derivs.hpp:808-841): d^m B_n / dT^m = 1/(n-2)! d^(n-1+m) alphar / dT^m drho^(n-1) at rho = 0.
 // One unit-seeded jet sweep at rho = 0 gives D_k = (1/T)^k d^k/d(1/T)^k of d^(n-1) alphar / drho^(n-1); with u = 1/T:
 //   dB/dT = -D_1 / T,   d2B/dT2 = (D_2 + 2 D_1) / T^2
@@ -596,6 +647,10 @@ int get_fugacity_coefficients_batch(const long long int uuid, const long long in
     return guarded(false, errmsg, errmsg_length, [&] { isochoric_call(*lookup(uuid), npts, T, rhovec, Ncomp, nullptr, nullptr, nullptr, nullptr, out, flags); });
 }
 
+int get_AtaudeltaXi_table_batch(const long long int uuid, const long long int npts, const double* tau, const double* delta, const double* molefrac,
+                                const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { if (npts > 0) ataudelta_table(*lookup(uuid), 1, 0, 0, 0, npts, tau, delta, molefrac, Ncomp, Ncomp * 36, out, flags); });
+}
 int get_dmBnvirdTm_batch(const long long int uuid, const int Nvir, const int NT, const long long int npts, const double* T, const double* molefrac,
                          const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length) {
     return guarded(false, errmsg, errmsg_length, [&] { if (npts > 0) virial_call(*lookup(uuid), Nvir, NT, npts, T, molefrac, Ncomp, out, flags); });

@@ -112,6 +112,11 @@ public:
     virtual void launch_virial_table(int, int, const DeviceBatch&, double*, cudaStream_t) const {
         throw NotImplementedError(std::string("virial coefficients are not implemented for model family ") + family());
     }
+    // get_AtaudeltaXi / XiXj / XiXjXk tables (derivs.hpp:341-414): in.T holds 1/tau, in.rho holds delta; which = 1: out as launch_ATrhoXi_table,
+    // 2: as launch_ATrhoXiXj_table (i, j), 3: as launch_ATrhoXiXjXk_table (i, j, k).  Only models with alphar_taudelta (multifluid).
+    virtual void launch_Ataudelta_table(int, const DeviceBatch&, int, int, int, double*, cudaStream_t) const {
+        throw NotImplementedError("Cannot take derivatives of a class that doesn't define the alphar_taudelta method");
+    }
     // IsochoricDerivatives::get_Psir_sigma_derivs (derivs.hpp:1496-1509): d^k Psir(T, rhovec + sigma v) / dsigma^k, k = 0..4;
     // in.x = rhovec rows, v[ncomp][npts], out[5][npts]
     virtual void launch_sigma_derivs(const DeviceBatch&, const double*, double*, cudaStream_t) const {
@@ -135,6 +140,7 @@ std::unique_ptr<Model> make_gerg_model(const std::string& kind, const Json& spec
 std::unique_ptr<Model> make_pcsaft_model(const Json& spec);
 std::unique_ptr<Model> make_saftvrmie_model(const Json& spec);
 std::unique_ptr<Model> make_genericsaft_model(const Json& spec);
+std::unique_ptr<Model> make_multifluid_model(const Json& spec);
 std::unique_ptr<Model> make_model(const Json& j);
 
 inline int grid_for(long long npts, int block, int max_blocks) {

@@ -21,6 +21,8 @@ void gergjet_launch_ATrhoXiXj(const GergProgram&, const DeviceBatch&, int, int, 
 void gergjet_launch_ATrhoXiXjXk(const GergProgram&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 void gergjet_launch_virial(const GergProgram&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);   // tq_ex_gergjet.cu
 void gergjet_launch_sigma(const GergProgram&, const DeviceBatch&, const double*, double*, cudaStream_t);
+void gergjet_launch_isochoric(const GergProgram&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void gergtd_launch(const GergProgram&, int which, const DeviceBatch&, int i, int j, int k, double* out, cudaStream_t);   // tq_ex_gergtd.cu
 
 namespace {
 
@@ -95,10 +97,18 @@ public:
     GergSource src;  // the term list the per-model kernels are generated from (tq_gerg_jit.hpp)
     std::vector<std::string> names;
     double Rgas = 8.314472;  // GERG.hpp:1175 (2008), :906 (2004)
-    std::string fam;
+    std::vector<double> Ri;  // per-fluid gas constants (multifluid, mole-fraction weighted)
+    std::string fam, meta_json = "{}";
+    std::string meta() const override { return meta_json; }
+    bool taudelta_ok() const { return fam == "multifluid"; }   // the reference's GERG2008ResidualModel has no alphar_taudelta (derivs.hpp:137-140)
     int ncomp() const override { return P.nc; }
     const char* family() const override { return fam.c_str(); }
-    double R(const double*, int) const override { return Rgas; }
+    double R(const double* x, int n) const override {
+        if (!P.r_weighted) return Rgas;
+        double r = 0;
+        for (int i = 0; i < n && i < P.nc; ++i) r += x[i] * Ri[i];   // MoleFractionWeighted::get_R (multifluid_gas_constant.hpp)
+        return r;
+    }
     const void* params_blob(size_t* n) const override { *n = sizeof(P); return &P; }
 
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gerg_launch_ATrhoXi(P, in, out, st); }
@@ -126,7 +136,14 @@ public:
     void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { gergjet_launch_virial(P, NT, ND, in, out, st); }
     void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { gergjet_launch_sigma(P, in, v, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
-        gerg_launch_isochoric(P, Rgas, in, o, st);
+        // the analytic kernel (tq_gerg_iso.cuh) knows tau^t temperature shapes and a constant R; JSON multifluid models with Gaussian /
+        // GaoB / Lemmon2005 terms or the mole-fraction-weighted R go through the jet sweeps
+        if (src.all_plain_tau && !P.r_weighted && !P.pure_shortcut) gerg_launch_isochoric(P, Rgas, in, o, st);
+        else gergjet_launch_isochoric(P, in, o, st);
+    }
+    void launch_Ataudelta_table(int which, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override {
+        if (!taudelta_ok()) throw NotImplementedError("Cannot take derivatives of a class that doesn't define the alphar_taudelta method");
+        gergtd_launch(P, which, in, i, j, k, out, st);
     }
     template<int NT, int ND> void launch(const DeviceBatch& in, double* out, cudaStream_t st) const {
         const size_t smem = (size_t)P.nw * kBlock * sizeof(double);
@@ -169,8 +186,13 @@ public:
         if (in.npts == 0) return;
         if (NT < 0 || ND < 0 || !shape_ok(NT, ND))
             throw InvalidArgument("derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is not a supported shape for " + fam);
+        if (NT > 0 && !src.all_plain_tau) {
+            // temperature derivatives of Gaussian / GaoB / Lemmon2005 temperature shapes are not binomial factors: jet sweep
+            gergjet_launch_virial(P, NT, ND, in, out, st);
+            return;
+        }
         static const bool interp = std::getenv("TEQPB200_GERG_INTERPRETER") != nullptr;  // A/B measurements only (profiles/)
-        if (!interp) {
+        if (!interp || P.ntf > 0 || P.pure_shortcut) {
             const Jit& j = specialised(NT, ND);
             jit_launch_table(j.k, j.s.consts, j.s.w_in_smem ? (size_t)j.s.nw * 128 * sizeof(double) : 0, in, out, st);
             return;
@@ -186,12 +208,11 @@ public:
 
 template<class F, class PR>
 std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string>& names_in, const F* fluids, size_t nfluids, const PR* pairs, size_t npairs) {
-    auto m = std::make_unique<GergModel>();
-    m->fam = fam;
-    GergProgram& P = m->P;
+    TermProgramInput in;
+    in.family = fam;
+    in.Rgas = 8.314472;   // GERG.hpp:1175 (2008), :906 (2004)
     const size_t N = names_in.size();
     if (N == 0) throw InvalidArgument("names must not be empty");
-    if (N > (size_t)kGergMaxC) throw InvalidArgument("too many components");
     std::vector<size_t> idx(N);
     for (size_t i = 0; i < N; ++i) {
         const std::string nm = lower(names_in[i]);
@@ -199,17 +220,14 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         for (size_t q = 0; q < nfluids; ++q) if (nm == fluids[q].name) { f = q; break; }
         if (f == nfluids) throw InvalidArgument("Unable to load pure info for " + names_in[i]);
         idx[i] = f;
-        m->names.push_back(nm);
+        in.names.push_back(nm);
+        in.Tc.push_back(fluids[f].Tc_K);
+        in.vc.push_back(1.0 / fluids[f].rhoc_molm3);
     }
     auto find_pair = [&](size_t a, size_t b) -> const PR& {
         for (size_t q = 0; q < npairs; ++q) if (pairs[q].i == a && pairs[q].j == b) return pairs[q];
         throw InvalidArgument(std::string("Unable to obtain BIP for the pair {") + fluids[a].name + "," + fluids[b].name + "}");
     };
-    P.nc = (int)N;
-    P.Rgas = m->Rgas;
-    for (size_t i = 0; i < N; ++i) { P.Tc[i] = fluids[idx[i]].Tc_K; P.vc[i] = 1.0 / fluids[idx[i]].rhoc_molm3; }
-
-    std::vector<RawTerm> raw;
     // pure-fluid terms (GERG.hpp:117-119)
     for (size_t i = 0; i < N; ++i) {
         const F& fl = fluids[idx[i]];
@@ -219,35 +237,72 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
             r.d = (int)fl.d[k]; r.l = (int)fl.l[k]; r.c = fl.c[k];
             r.kind = (r.c == 0.0) ? GG_POLY : GG_EXP;
             if (r.kind == GG_POLY) r.l = 0;
-            raw.push_back(r);
+            in.pure.push_back(r);
         }
     }
     // reducing pairs and departure terms
-    int pidx = 0, ndep = 0;
     for (size_t i = 0; i < N; ++i) {
-        for (size_t j = i + 1; j < N; ++j, ++pidx) {
+        for (size_t j = i + 1; j < N; ++j) {
             if (idx[i] == idx[j]) throw InvalidArgument("duplicate component " + names_in[i]);
             const bool fwd = idx[i] < idx[j];
             const PR& pr = fwd ? find_pair(idx[i], idx[j]) : find_pair(idx[j], idx[i]);
+            TermProgramInput::Pair q;
             // reversed order: reciprocal betas (GERG.hpp:757-763)
-            const double bT = fwd ? pr.betaT : 1 / pr.betaT, bV = fwd ? pr.betaV : 1 / pr.betaV;
-            const double Tci = P.Tc[i], Tcj = P.Tc[j], vci = P.vc[i], vcj = P.vc[j];
-            const double YT = bT * pr.gammaT * std::sqrt(Tci * Tcj);
-            const double s = std::cbrt(vci) + std::cbrt(vcj);
-            const double YV = 1.0 / 8.0 * bV * pr.gammaV * (s * s * s);
-            P.pair[pidx].beta2T = bT * bT; P.pair[pidx].YT2 = 2.0 * YT;
-            P.pair[pidx].beta2V = bV * bV; P.pair[pidx].YV2 = 2.0 * YV;
+            q.betaT = fwd ? pr.betaT : 1 / pr.betaT; q.betaV = fwd ? pr.betaV : 1 / pr.betaV;
+            q.gammaT = pr.gammaT; q.gammaV = pr.gammaV; q.F = pr.Fij;
             if (pr.Fij != 0.0) {
-                if (ndep >= kGergMaxDep) throw InvalidArgument("too many departure pairs");
-                P.dep_i[ndep] = (unsigned char)i; P.dep_j[ndep] = (unsigned char)j; P.depF[ndep] = pr.Fij;
                 for (size_t k = 0; k < pr.n.size(); ++k) {
                     RawTerm r{};
-                    r.w = (int)N + ndep; r.n = pr.n[k]; r.t = pr.t[k]; r.d = (int)pr.d[k];
+                    r.n = pr.n[k]; r.t = pr.t[k]; r.d = (int)pr.d[k];
                     r.eta = pr.eta[k]; r.eps = pr.epsilon[k]; r.beta = pr.beta[k]; r.gamma = pr.gamma[k];
                     if (r.eta == 0.0 && r.beta == 0.0) { r.kind = GG_POLY; r.eps = r.gamma = 0; }
                     else r.kind = GG_GAUSS;
-                    raw.push_back(r);
+                    q.terms.push_back(r);
                 }
+            }
+            in.pairs.push_back(std::move(q));
+        }
+    }
+    return make_term_program_model(in);
+}
+
+}  // namespace
+
+// Compiles a term list into the device term program (groups x temperature shapes x terms) shared by every kernel of the family
+std::unique_ptr<Model> make_term_program_model(const TermProgramInput& in) {
+    auto m = std::make_unique<GergModel>();
+    m->fam = in.family;
+    m->names = in.names;
+    m->meta_json = in.meta;
+    GergProgram& P = m->P;
+    const size_t N = in.names.size();
+    if (N == 0) throw InvalidArgument("at least one component is needed");
+    if (N > (size_t)kGergMaxC) throw InvalidArgument("too many components (the device term program holds " + std::to_string(kGergMaxC) + ")");
+    if (in.pairs.size() != N * (N - 1) / 2) throw InvalidArgument("internal: pair list does not match the component count");
+    P.nc = (int)N;
+    m->Rgas = in.Rgas;
+    P.Rgas = in.Rgas;
+    P.r_weighted = in.r_weighted ? 1 : 0;
+    P.limit_form = in.limit_form ? 1 : 0;
+    P.pure_shortcut = (in.pure_shortcut && N == 1) ? 1 : 0;
+    m->Ri = in.Ri;
+    for (size_t i = 0; i < N; ++i) { P.Tc[i] = in.Tc[i]; P.vc[i] = in.vc[i]; if (in.r_weighted) P.Ri[i] = in.Ri.at(i); }
+
+    std::vector<RawTerm> raw = in.pure;
+    int pidx = 0, ndep = 0;
+    for (size_t i = 0; i < N; ++i) {
+        for (size_t j = i + 1; j < N; ++j, ++pidx) {
+            const TermProgramInput::Pair& pr = in.pairs[pidx];
+            const double Tci = P.Tc[i], Tcj = P.Tc[j], vci = P.vc[i], vcj = P.vc[j];
+            const double YT = pr.betaT * pr.gammaT * std::sqrt(Tci * Tcj);
+            const double s = std::cbrt(vci) + std::cbrt(vcj);
+            const double YV = 1.0 / 8.0 * pr.betaV * pr.gammaV * (s * s * s);
+            P.pair[pidx].beta2T = pr.betaT * pr.betaT; P.pair[pidx].YT2 = 2.0 * YT;
+            P.pair[pidx].beta2V = pr.betaV * pr.betaV; P.pair[pidx].YV2 = 2.0 * YV;
+            if (pr.F != 0.0 && !pr.terms.empty()) {
+                if (ndep >= kGergMaxDep) throw InvalidArgument("too many departure pairs");
+                P.dep_i[ndep] = (unsigned char)i; P.dep_j[ndep] = (unsigned char)j; P.depF[ndep] = pr.F;
+                for (RawTerm r : pr.terms) { r.w = (int)N + ndep; raw.push_back(r); }
                 ++ndep;
             }
         }
@@ -256,18 +311,33 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
     {
         GergSource& S = m->src;
         S.nc = (int)N; S.ndep = ndep;
+        S.pure_shortcut = P.pure_shortcut != 0;
         S.Tc.assign(P.Tc, P.Tc + N); S.vc.assign(P.vc, P.vc + N);
         S.pair.assign(P.pair, P.pair + pidx);
         for (int q = 0; q < ndep; ++q) { S.dep_i.push_back(P.dep_i[q]); S.dep_j.push_back(P.dep_j[q]); S.depF.push_back(P.depF[q]); }
         S.terms = raw;
+        for (const auto& r : raw) if (r.tk != GT_PLAIN) S.all_plain_tau = false;
     }
 
-    // group by density shape, then by tau exponent
+    // non-plain temperature shapes
+    std::map<GergTauKey, int> tfidx;   // (ignoring t) -> 1 + index into P.tf
+    auto tf_of = [&](const RawTerm& r) -> int {
+        if (r.tk == GT_PLAIN) return 0;
+        const GergTauKey k{0.0, r.tk, r.tp1, r.tp2, r.tp3};
+        auto it = tfidx.find(k);
+        if (it != tfidx.end()) return it->second;
+        if (P.ntf >= kGergMaxTF) throw InvalidArgument("too many distinct temperature shapes (Gaussian / GaoB / Lemmon2005 terms) for the device term program");
+        P.tf[P.ntf] = GergTauFn{r.tk, 0, r.tp1, r.tp2, r.tp3};
+        tfidx[k] = ++P.ntf;
+        return P.ntf;
+    };
+
+    // group by density shape, then by temperature shape
     // key = (exponent shape h, then d): groups that share h are consecutive, d ascending (running product of delta)
     using GKey = std::tuple<int, int, double, double, double, double, double, int>;
-    std::map<GKey, std::map<double, std::vector<const RawTerm*>>> groups;
-    for (const auto& r : raw) groups[GKey{r.kind, r.l, r.c, r.eta, r.eps, r.beta, r.gamma, r.d}][r.t].push_back(&r);
-    if (groups.size() > (size_t)kGergMaxGroup) throw InvalidArgument("too many distinct density groups");
+    std::map<GKey, std::map<GergTauKey, std::vector<const RawTerm*>>> groups;
+    for (const auto& r : raw) groups[GKey{r.kind, r.l, r.c, r.eta, r.eps, r.beta, r.gamma, r.d}][tau_key(r)].push_back(&r);
+    if (groups.size() > (size_t)kGergMaxGroup) throw InvalidArgument("too many distinct density groups (" + std::to_string(groups.size()) + ") for the device term program");
     int g = 0, tq = 0, term = 0, rec = 0;
     for (const auto& [key, bytau] : groups) {
         GergGroup& G = P.group[g];
@@ -281,12 +351,13 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
         }
         for (int mm = 1; mm <= kGergND; ++mm) { G.bd[mm - 1] = binom_real(G.d, mm); G.bl[mm - 1] = binom_real(G.l, mm); }
         G.ntq = (int)bytau.size();
-        for (const auto& [t, terms] : bytau) {
+        for (const auto& [tkey, terms] : bytau) {
+            const double t = std::get<0>(tkey);
             const int rest = (int)terms.size() - 1, npair = (rest + 1) / 2;
             if (rec + 2 + 2 * npair > kGergMaxRec) throw InvalidArgument("too many terms for the device term program");
             if (!(std::fabs(t) <= kGergMaxAbsT)) throw InvalidArgument("temperature exponent out of the device term program's range");
             P.rec[rec] = GergRec{t, npair, terms[0]->w * kGergWS * 8};
-            P.rec[rec + 1] = GergRec{terms[0]->n, 0, 0};
+            P.rec[rec + 1] = GergRec{terms[0]->n, tf_of(*terms[0]), 0};
             rec += 2;
             for (int k = 0; k < 2 * npair; ++k, ++rec)
                 P.rec[rec] = (k < rest) ? GergRec{terms[k + 1]->n, terms[k + 1]->w * kGergWS * 8, 0} : GergRec{0.0, 0, 0};
@@ -299,6 +370,7 @@ std::unique_ptr<Model> build_gerg(const char* fam, const std::vector<std::string
     return m;
 }
 
+namespace {
 }  // namespace
 
 std::unique_ptr<Model> make_gerg_model(const std::string& kind, const Json& spec) {

@@ -39,6 +39,15 @@ struct GergRedPair {       // reducing-function data of the pair (i<j), in lexic
 
 enum GergGroupKind : int { GG_POLY = 0, GG_EXP = 1, GG_GAUSS = 2 };
 
+// Temperature shape of a term: F(tau) = tau^t exp(h(tau)).  GERG-2004/2008 only has GT_PLAIN; the JSON-driven multifluid models
+// (/root/reference/include/teqp/models/multifluid_eosterms.hpp) add
+//   GT_GAUSS   h = -p1 (tau - p2)^2               GaussianEOSTerm :139-165 (beta, gamma)
+//   GT_GAOB    h = 1 / (p1 (tau - p2)^2 + p3)     GaoBEOSTerm :199-243 (beta, gamma, b)
+//   GT_POWEXP  h = -p1 tau^p2                      Lemmon2005EOSTerm :171-193 (1, m), DoubleExponentialEOSTerm :108-133 (gt, lt)
+enum GergTauKind : int { GT_PLAIN = 0, GT_GAUSS = 1, GT_GAOB = 2, GT_POWEXP = 3 };
+struct GergTauFn { int kind, pad_; double p1, p2, p3; };
+constexpr int kGergMaxTF = 40;   // distinct non-plain temperature shapes per model
+
 struct GergGroup {
     int kind;        // GG_POLY: delta^d ; GG_EXP: delta^d exp(-c delta^l) ; GG_GAUSS: delta^d exp(-eta(delta-eps)^2 - beta(delta-gamma))
     int d, l;        // integer exponents
@@ -53,7 +62,7 @@ struct GergGroup {
 
 // The (g,t) sums are one stream of 16-byte units, read front to back with warp-uniform addresses:
 //   (g,t) header, 2 units: {val = t, a = number of term PAIRS that follow, b = byte offset of the first term's weight}
-//                          {val = n of the first term}
+//                          {val = n of the first term, a = 1 + index into tf[] of the temperature shape, 0 = plain tau^t}
 //   then per further term  {val = n, a = byte offset of its weight}, padded with {0, 0} to an even count
 // (62 of the 109 (g,t) sums of the 10-component natural gas have a single term: no inner loop for those)
 struct alignas(16) GergRec {
@@ -71,8 +80,15 @@ struct GergProgram {
     GergRedPair pair[kGergMaxPair];
     GergGroup group[kGergMaxGroup];
     GergRec rec[kGergMaxRec];
+    // ---- JSON-driven multifluid extensions (all zero for the GERG kinds) ----
+    int ntf;            // non-plain temperature shapes in tf[]
+    int r_weighted;     // 1: R(x) = sum_i x_i Ri[i] (multifluid.hpp:973); 0: Rgas
+    int limit_form;     // 1: a reducing pair whose denominator is zero contributes its limit form (multifluid_reducing.hpp:234-237); 0: skipped (GERG.hpp:189)
+    int pure_shortcut;  // 1: single component: the mole fraction does not multiply the pure-fluid sum (multifluid.hpp:172-175)
+    double Ri[kGergMaxC];
+    GergTauFn tf[kGergMaxTF];
 };
-static_assert(sizeof(GergProgram) <= 32000, "GergProgram must fit in the 32 KB kernel-parameter space");
+static_assert(sizeof(GergProgram) <= 32600, "GergProgram must fit in the 32 KB kernel-parameter space (32764 B)");
 
 TQ_HD double wload(const double* W, int byte_offset) {
     return *reinterpret_cast<const double*>(reinterpret_cast<const char*>(W) + byte_offset);

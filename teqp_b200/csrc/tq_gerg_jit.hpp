@@ -11,7 +11,9 @@
 //     alphar = sum_shapes  E_h(s) * B_h(s),   E_h = Taylor coefficients of exp(h(delta (1+s))),
 //     B_h[j] = sum_{groups g of shape h} binom(d_g, j) delta^d_g C_g,      C_g = sum_t tau^t sum_{terms (g,t)} n W_w(x)
 #pragma once
+#include <memory>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "tq_gerg.cuh"
@@ -21,14 +23,20 @@ namespace tq {
 struct GergTerm {
     int w;        // weight index: component i, or nc + q for departure pair q
     double n, t;
-    int kind;     // GergGroupKind
+    int kind;     // GergGroupKind (density shape)
     int d, l;
     double c, eta, eps, beta, gamma;
+    int tk = 0;   // GergTauKind (temperature shape), parameters tp1..tp3 (tq_gerg.cuh)
+    double tp1 = 0, tp2 = 0, tp3 = 0;
 };
+using GergTauKey = std::tuple<double, int, double, double, double>;  // t, tk, tp1, tp2, tp3
+inline GergTauKey tau_key(const GergTerm& r) { return GergTauKey{r.t, r.tk, r.tp1, r.tp2, r.tp3}; }
 
 // everything the generator needs, in the reference's order (pairs lexicographic i<j)
 struct GergSource {
     int nc = 0, ndep = 0;
+    bool pure_shortcut = false;   // single-component multifluid: the mole fraction does not multiply the sum (multifluid.hpp:172-175)
+    bool all_plain_tau = true;    // no term has a non-plain temperature shape (then temperature derivatives are binomial factors)
     std::vector<double> Tc, vc;
     std::vector<GergRedPair> pair;
     std::vector<int> dep_i, dep_j;
@@ -48,6 +56,24 @@ struct JitSource {
 // straight-line source for the Lambda^r table of shape (NT, ND).  NT == 0: tau^t once per distinct t, per-group accumulators in
 // registers; NT > 0: groups one after the other, tau^t per (group, t), temperature orders by t (t-1) ... /n!
 JitSource gerg_generate(const GergSource& src, int NT, int ND);
+
+// What a corresponding-states term-program model is built from (GERG-2004/2008 tables, or the JSON-driven multifluid kind)
+struct TermProgramInput {
+    std::string family;
+    std::vector<std::string> names;
+    std::vector<double> Tc, vc;          // reducing temperature, reducing molar volume (1/rho_r)
+    struct Pair {                        // pairs (i < j) in lexicographic order, betas oriented for (i, j)
+        double betaT = 1, gammaT = 1, betaV = 1, gammaV = 1, F = 0;
+        std::vector<GergTerm> terms;     // departure function terms (w is filled in by the builder)
+    };
+    std::vector<Pair> pairs;
+    std::vector<GergTerm> pure;          // w = component index
+    double Rgas = 0;                     // constant gas constant ...
+    std::vector<double> Ri;              // ... or per-fluid values, mole-fraction weighted when r_weighted
+    bool r_weighted = false, limit_form = false, pure_shortcut = false;
+    std::string meta = "{}";
+};
+std::unique_ptr<Model> make_term_program_model(const TermProgramInput& in);
 
 // ---- NVRTC runtime (tq_jit.cu) ------------------------------------------------------------------------------------------
 struct JitKernel;  // opaque: a loaded cubin + kernel handle

@@ -173,6 +173,34 @@ class Model:
     def get_fugacity_coefficients_batch(self, T, rhovec, out=None):
         return self._iso(lib().get_fugacity_coefficients_batch, T, rhovec, [rhovec.shape[0]], out)[0]
 
+    def get_AtaudeltaXi_table_batch(self, tau, delta, x):
+        """[Ncomp][3][3][4][npts]: index (i, Ntau, Ndelta, NXi); multifluid models only (derivs.hpp:341-351)"""
+        tau = np.ascontiguousarray(tau, dtype=np.float64); delta = np.ascontiguousarray(delta, dtype=np.float64); x = np.ascontiguousarray(x, dtype=np.float64)
+        n = tau.size; nc = x.shape[0]
+        flags = BROADCAST_X if x.ndim == 1 else 0
+        out = np.empty((nc, 3, 3, 4, n))
+        err = C.create_string_buffer(2000)
+        _check(lib().get_AtaudeltaXi_table_batch(self._uuid, C.c_longlong(n), tau.ctypes.data_as(_dp), delta.ctypes.data_as(_dp), x.ctypes.data_as(_dp), C.c_int(nc),
+                                                 out.ctypes.data_as(_dp), C.c_int(flags), err, C.c_int(2000)), err)
+        return out
+
+    def _taudelta_scalar(self, fn, tau, Ntau, delta, Ndelta, molefrac, *idx):
+        z = np.ascontiguousarray(molefrac, dtype=np.float64)
+        out = C.c_double()
+        err = C.create_string_buffer(2000)
+        _check(fn(self._uuid, C.c_double(tau), C.c_int(Ntau), C.c_double(delta), C.c_int(Ndelta), z.ctypes.data_as(_dp), C.c_int(z.size),
+                  *[C.c_int(v) for v in idx], C.byref(out), err, C.c_int(2000)), err)
+        return out.value
+
+    def get_AtaudeltaXi(self, tau, Ntau, delta, Ndelta, molefrac, i, NXi):
+        return self._taudelta_scalar(lib().get_AtaudeltaXi, tau, Ntau, delta, Ndelta, molefrac, i, NXi)
+
+    def get_AtaudeltaXiXj(self, tau, Ntau, delta, Ndelta, molefrac, i, NXi, j, NXj):
+        return self._taudelta_scalar(lib().get_AtaudeltaXiXj, tau, Ntau, delta, Ndelta, molefrac, i, NXi, j, NXj)
+
+    def get_AtaudeltaXiXjXk(self, tau, Ntau, delta, Ndelta, molefrac, i, NXi, j, NXj, k, NXk):
+        return self._taudelta_scalar(lib().get_AtaudeltaXiXjXk, tau, Ntau, delta, Ndelta, molefrac, i, NXi, j, NXj, k, NXk)
+
     def get_dmBnvirdTm_batch(self, Nvir, NT, T, x, out=None):
         """d^NT B_Nvir / dT^NT for an array of temperatures (VirialDerivatives::get_dmBnvirdTm, derivs.hpp:780-841); x: [Ncomp][npts] or [Ncomp]"""
         dev = _is_torch(T)

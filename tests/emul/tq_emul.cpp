@@ -146,6 +146,11 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
         const void* blob = m->params_blob(&nb);
         const std::string fam = m->family();
         const long long xs = broadcast ? 0 : npts;
+        if (fam == "multifluid") {   // JSON multifluid: the jet sweep (what the product runs where the generated kernel does not apply)
+            const GergProgram& P = *static_cast<const GergProgram*>(blob);
+            generic_table<GergJetDev>(P, P.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
         if (fam.rfind("GERG", 0) == 0) {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
 #define C(a, b) if (NT == a && ND == b) { gerg_loop<a, b>(P, npts, T, rho, x, xs, out); return 0; }
@@ -197,6 +202,23 @@ int emul_extras(const char* json, int what, int NT, int ND, long long npts, cons
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
 }
 
+// get_AtaudeltaXi table (which = 1; layout of emul_ATrhoXi_table), XiXj (2), XiXjXk (3): multifluid only; tau, delta given
+int emul_Ataudelta(const char* json, int which, int i, int j, int k, long long npts, const double* tau, const double* delta, const double* x, int ncomp,
+                   double* out, char* err, int errlen) {
+    try {
+        auto m = tq::make_model(Json::parse(json));
+        if (ncomp != m->ncomp()) throw InvalidArgument("wrong number of components");
+        if (std::string(m->family()) != "multifluid") throw NotImplementedError("Cannot take derivatives of a class that doesn't define the alphar_taudelta method");
+        size_t nb = 0;
+        const GergProgram& P = *static_cast<const GergProgram*>(m->params_blob(&nb));
+        std::vector<double> Tinv((size_t)npts);
+        for (long long q = 0; q < npts; ++q) Tinv[q] = 1.0 / tau[q];
+        if (which == 1) generic_atrhoxi<GergTauDeltaDev>(P, ncomp, npts, Tinv.data(), delta, x, out);
+        else generic_xx<GergTauDeltaDev>(P, ncomp, which, i, j, k, npts, Tinv.data(), delta, x, out);
+        return 0;
+    } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
 int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const double* rho, const double* x, int ncomp, double* out,
                        char* err, int errlen) {
     try {
@@ -207,7 +229,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
-        else if (fam.rfind("GERG", 0) == 0) generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_atrhoxi<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
@@ -223,7 +245,7 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         const void* blob = m->params_blob(&nb);
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
-        else if (fam.rfind("GERG", 0) == 0) generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -242,7 +264,7 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         o.chempotVLE = outs[6]; o.dchempotdT = outs[7]; o.dlnphi_dT = outs[8]; o.dlnphi_drho = outs[9]; o.dlnphi_dv = outs[10]; o.dlnphi_dx = outs[11];
         if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
-        else if (fam.rfind("GERG", 0) == 0) generic_ip<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_ip<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rhovec, o);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -260,7 +282,12 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
-        else if (fam.rfind("GERG", 0) == 0) gerg_iso_loop(*static_cast<const GergProgram*>(blob), m->R(nullptr, 0), npts, T, rhovec, o);
+        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
+            const GergProgram& P = *static_cast<const GergProgram*>(blob);
+            // same dispatch as GergModel::launch_isochoric: analytic kernel for tau^t shapes and a constant R, jet sweeps otherwise
+            if (P.ntf == 0 && !P.r_weighted && !P.pure_shortcut) gerg_iso_loop(P, P.Rgas, npts, T, rhovec, o);
+            else generic_iso<GergJetDev>(P, ncomp, npts, T, rhovec, o);
+        }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }

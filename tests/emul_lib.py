@@ -114,6 +114,18 @@ def virial_table(spec, NT, ND, T, x):
     return out.reshape(NT + 1, ND + 1, n)
 
 
+def Ataudelta_table(spec, tau, delta, x):
+    tau = np.ascontiguousarray(tau, dtype=np.float64); delta = np.ascontiguousarray(delta, dtype=np.float64); x = np.ascontiguousarray(x, dtype=np.float64)
+    n = tau.size; nc = x.shape[0]
+    out = np.empty((nc * 36, n))
+    err = C.create_string_buffer(1000)
+    rc = lib().emul_Ataudelta(json.dumps(spec).encode(), C.c_int(1), C.c_int(0), C.c_int(0), C.c_int(0), C.c_longlong(n), _p(tau), _p(delta), _p(x), C.c_int(nc),
+                              _p(out), err, C.c_int(1000))
+    if rc:
+        raise RuntimeError(err.value.decode())
+    return out.reshape(nc, 3, 3, 4, n)
+
+
 def dmBnvirdTm(spec, Nvir, NT, T, x):
     """the combination libteqpb200's virial_call forms from the table (csrc/tq_capi.cu)"""
     import math

@@ -144,6 +144,15 @@ class RefModel:
         self._call(lib().ref_Psir_fgradHessian, C.c_int(0), C.c_longlong(n), _p(T), _p(rv), C.c_int(nc), _p(f), _p(g), _p(H))
         return f, g, H
 
+    def Ataudelta(self, which, Ntau, Ndelta, idx, tau, delta, x):
+        """which 1: get_AtaudeltaXi idx = (i, NXi); 2: XiXj idx = (i, NXi, j, NXj); 3: XiXjXk idx = (i, NXi, j, NXj, k, NXk)"""
+        tau = np.ascontiguousarray(tau, dtype=np.float64); delta = np.ascontiguousarray(delta, dtype=np.float64)
+        n = tau.size; x = _soa(x, n)
+        out = np.empty(n)
+        ii = (C.c_int * 6)(*(list(idx) + [0] * (6 - len(idx))))
+        self._call(lib().ref_get_Ataudelta, C.c_int(which), C.c_int(Ntau), C.c_int(Ndelta), ii, C.c_longlong(n), _p(tau), _p(delta), _p(x), C.c_int(x.shape[0]), _p(out))
+        return out
+
     def dmBnvirdTm(self, Nvir, NT, T, x):
         T = np.ascontiguousarray(T, dtype=np.float64)
         n = T.size

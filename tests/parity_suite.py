@@ -20,10 +20,14 @@ class EmulBackend:
         self.e = emul
 
     def ar_table(self, spec, NT, ND, T, rho, x):
-        if spec["kind"].startswith("GERG") and T.size:
+        if (spec["kind"].startswith("GERG") or spec["kind"] == "multifluid") and T.size:
             # the product evaluates GERG tables with the per-model GENERATED kernel: replay that source (compiled for the host) -- the
             # interpreter kernel's per-point function is replayed as well and must agree to the parity rule
-            return self.e.jit_ar_table(spec, NT, ND, T, rho, x)
+            try:
+                return self.e.jit_ar_table(spec, NT, ND, T, rho, x)
+            except RuntimeError as e:   # temperature derivatives of non-plain temperature shapes: the product runs the jet sweep there too
+                if "jet sweep" not in str(e):
+                    raise
         return self.e.ar_table(spec, NT, ND, T, rho, x)
 
     def ATrhoXi_table(self, spec, T, rho, x):
@@ -37,6 +41,9 @@ class EmulBackend:
 
     def dmBnvirdTm(self, spec, Nvir, NT, T, x):
         return self.e.dmBnvirdTm(spec, Nvir, NT, T, x)
+
+    def Ataudelta_table(self, spec, tau, delta, x):
+        return self.e.Ataudelta_table(spec, tau, delta, x)
 
     def sigma_derivs(self, spec, T, rv, v):
         return self.e.sigma_derivs(spec, T, rv, v)
@@ -84,6 +91,9 @@ class GpuBackend:
     def dmBnvirdTm(self, spec, Nvir, NT, T, x):
         return self.model(spec).get_dmBnvirdTm_batch(Nvir, NT, T, x)
 
+    def Ataudelta_table(self, spec, tau, delta, x):
+        return self.model(spec).get_AtaudeltaXi_table_batch(tau, delta, x)
+
     def sigma_derivs(self, spec, T, rv, v):
         return self.model(spec).get_Psir_sigma_derivs_batch(T, rv, v)
 
@@ -108,11 +118,31 @@ class GpuBackend:
 # No second implementation can be closer to the reference than the reference is to the exact value of its own formulas, so these
 # families get ATOL = 2 x (sum of the two columns) as an additional absolute floor (in coefficient space, i.e. times n! m!).
 ATOL_FAMILY = {"MIE1": 1.3e-13, "MIE3": 1.3e-13, "GSAFT_CR1": 3e-13, "GSAFT_C4": 5e-12, "GSAFT_WATER": 8e-11}
-ADJ_FACTOR = {"MIE1": 3.0, "MIE3": 3.0, "GSAFT_C4": 3.0, "GSAFT_CR1": 3.0, "GSAFT_WATER": 3.0}
+ADJ_FACTOR = {"MIE1": 3.0, "MIE3": 3.0, "GSAFT_C4": 3.0, "GSAFT_CR1": 3.0, "GSAFT_WATER": 3.0,
+              "MF_R32_R125": 10.0}   # orders 5 and 6 of get_Ar06n only (density exponents up to 8 through binomials): 1.3e-14 S against the reference's 1.6e-15 S
 
 
-def ftol_for(name):
-    return parity.FTOL
+# The cubic family: alphar = -ln(1 - b rho) - ... is evaluated by the reference exactly so, and at low density 1 - b rho rounds with a
+# relative error eps, i.e. ln(1 - b rho) ~ -b rho carries a relative error eps / (b rho).  Measured (tools/adjudicate.py, C1): the
+# reference's Ar00 / Ar10 / Ar20 sit 1.3e-12 / 1.9e-12 / 4.4e-13 S from the binary128 truth (every order that differentiates the density
+# is at 5e-16 S).  The host replay reproduces those roundings bit for bit (same libm); the GPU's log differs from glibc's in the last
+# bit, which this cancellation amplifies to the same 1e-12 S -- so the density-order-0 outputs of the cubic family get 4e-12 S.
+CUBIC_NAMES = ("PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2")
+CUBIC_FTOL_D0 = 4e-12
+
+
+# Reference-quality multifluid EOS carry critical-region Gaussian terms exp(-eta (delta - eps)^2 - beta (tau - gamma)^2) with eta, beta of
+# several hundred: each temperature / density derivative multiplies the rounding noise of the exponent by ~2 beta tau (tau - gamma).
+# Measured against the binary128 evaluation of the reference's own MultiFluid templates (tools/adjudicate.py, 1500 points): the
+# reference's double-precision Lambda_nm sit up to this many S from the exact value (worst entries Ar23 / Ar24 / Ar40), the kernels no
+# farther.  The floor coefficient for these models is 4x that noise.
+REF_NOISE_S = {"MF_CH4_N2_O2": 3.3e-13, "MF_CH4_C2H6_CODATA": 1.7e-12, "MF_N2": 2.1e-13}
+
+
+def ftol_for(name, density_order=None):
+    if name in CUBIC_NAMES and (density_order is None or density_order == 0):
+        return CUBIC_FTOL_D0
+    return max(parity.FTOL, 4.0 * REF_NOISE_S.get(name, 0.0))
 
 
 def extra_scale(name):
@@ -138,17 +168,17 @@ def ar_tables(be, oracle, name, n=3000):
     got = be.ar_table(spec, 2, 4, T, rho, x)
     for i in range(3):
         for j in range(5):
-            parity.check("%s Ar%d%d" % (name, i, j), got[i, j], ref[i, j], fam * parity.fact(i, j), ftol=ft, max_floor_frac=floor_limit(name, i + j))
+            parity.check("%s Ar%d%d" % (name, i, j), got[i, j], ref[i, j], fam * parity.fact(i, j), ftol=ftol_for(name, j), max_floor_frac=floor_limit(name, i + j))
     g40 = be.ar_table(spec, 4, 0, T, rho, x)[:, 0]
     for k in range(5):
-        parity.check("%s Ar%d0n" % (name, k), g40[k], r40[k], fam * parity.fact(k), ftol=ft, max_floor_frac=floor_limit(name, k))
+        parity.check("%s Ar%d0n" % (name, k), g40[k], r40[k], fam * parity.fact(k), ftol=ftol_for(name, 0), max_floor_frac=floor_limit(name, k))
     g06 = be.ar_table(spec, 0, 6, T, rho, x)[0]
     for k in range(7):
-        parity.check("%s Ar0%dn" % (name, k), g06[k], r06[k], fam * parity.fact(k), ftol=ft, max_floor_frac=floor_limit(name, k))
+        parity.check("%s Ar0%dn" % (name, k), g06[k], r06[k], fam * parity.fact(k), ftol=ftol_for(name, k), max_floor_frac=floor_limit(name, k))
     # the headline call itself: get_Ar04n
     g04 = be.ar_table(spec, 0, 4, T, rho, x)[0]
     for k in range(5):
-        parity.check("%s Ar04n[%d]" % (name, k), g04[k], r06[k], fam * parity.fact(k), ftol=ft, max_floor_frac=floor_limit(name, k))
+        parity.check("%s Ar04n[%d]" % (name, k), g04[k], r06[k], fam * parity.fact(k), ftol=ftol_for(name, k), max_floor_frac=floor_limit(name, k))
 
 
 COMBOS_ATRHOXI = [(0, 0, 1), (0, 0, 2), (0, 0, 3), (1, 0, 0), (1, 0, 1), (1, 0, 2), (1, 0, 3), (0, 1, 0), (0, 1, 1), (0, 1, 2), (0, 1, 3),
@@ -172,7 +202,7 @@ def atrhoxi(be, oracle, name, n=400):
     for (NT, ND, NX) in COMBOS_ATRHOXI:
         S = np.maximum(parity.family_scale(ref[:, :NT + 1, :ND + 1, :NX + 1], (0, 1, 2, 3)), extra_scale(name))
         for i in range(nc):
-            parity.check("%s ATrhoXi NT%d ND%d X%d^%d" % (name, NT, ND, i, NX), got[i, NT, ND, NX], ref[i, NT, ND, NX], S, ftol=ft * (1 + NX),
+            parity.check("%s ATrhoXi NT%d ND%d X%d^%d" % (name, NT, ND, i, NX), got[i, NT, ND, NX], ref[i, NT, ND, NX], S, ftol=2 * ftol_for(name, ND) * 2**NX,   # nested jets: each composition order doubles the rounding noise
                          max_floor_frac=floor_limit(name, NT + ND + NX))
 
 
@@ -195,7 +225,7 @@ def cross_composition(be, oracle, name, n=200):
         refs = {c: m.ATrhoXiXj(c[0], c[1], i, c[2], j, c[3], T, rho, x) for c in COMBOS_XIXJ}
         for c in COMBOS_XIXJ:
             S = np.maximum(np.max([np.abs(refs[d]) for d in COMBOS_XIXJ if d[0] <= c[0] and d[1] <= c[1]], axis=0), extra_scale(name))
-            parity.check("%s ATrhoXiXj NT%d ND%d x%d^%d x%d^%d" % (name, c[0], c[1], i, c[2], j, c[3]), got[c[0], c[1], c[2], c[3]], refs[c], S, ftol=3 * ft,
+            parity.check("%s ATrhoXiXj NT%d ND%d x%d^%d x%d^%d" % (name, c[0], c[1], i, c[2], j, c[3]), got[c[0], c[1], c[2], c[3]], refs[c], S, ftol=3 * ftol_for(name, c[1]),
                          max_floor_frac=floor_limit(name, sum(c)))
     if nc >= 3:
         for (i, j, k) in [(0, 1, 2), (nc - 1, 0, 1)]:
@@ -203,7 +233,7 @@ def cross_composition(be, oracle, name, n=200):
             refs = {c: m.ATrhoXiXjXk(c[0], c[1], i, c[2], j, c[3], k, c[4], T, rho, x) for c in COMBOS_XIXJXK}
             for c in COMBOS_XIXJXK:
                 S = np.maximum(np.max([np.abs(refs[d]) for d in COMBOS_XIXJXK if d[0] <= c[0] and d[1] <= c[1]], axis=0), extra_scale(name))
-                parity.check("%s ATrhoXiXjXk NT%d ND%d %d%d%d" % (name, c[0], c[1], c[2], c[3], c[4]), got[c[0], c[1], c[2], c[3], c[4]], refs[c], S, ftol=4 * ft,
+                parity.check("%s ATrhoXiXjXk NT%d ND%d %d%d%d" % (name, c[0], c[1], c[2], c[3], c[4]), got[c[0], c[1], c[2], c[3], c[4]], refs[c], S, ftol=4 * ftol_for(name, c[1]),
                              max_floor_frac=floor_limit(name, sum(c)))
 
 
@@ -212,20 +242,21 @@ def isochoric(be, oracle, name, n=600, lnphi=True):
     rv = np.ascontiguousarray(x * rho)
     m = oracle.RefModel(spec)
     rf, rg, rH = m.fgradHessian(T, rv)
+    ft = ftol_for(name, 1)
     nc = rv.shape[0]
     rH = rH.reshape(nc, nc, -1)
     f, g, H, lp, ph = be.isochoric(spec, T, rv)
     sg = np.maximum(parity.family_scale(rg, 0), extra_scale(name) * m.get_R(x[:, 0]) * T)
-    parity.check(name + " Psir", f, rf, np.maximum(np.max(np.abs(rg * rv), axis=0), sg * rho))
-    parity.check(name + " grad Psir", g, rg, sg)
+    parity.check(name + " Psir", f, rf, np.maximum(np.max(np.abs(rg * rv), axis=0), sg * rho), ftol=ft)
+    parity.check(name + " grad Psir", g, rg, sg, ftol=ft)
     # rho_j * H_ij has the units of the gradient: scale the Hessian rows by that
     sH = np.maximum(parity.family_scale(rH, (0, 1)), sg / np.min(rv, axis=0))
-    parity.check(name + " Hessian Psir", H, rH, sH)
+    parity.check(name + " Hessian Psir", H, rH, sH, ftol=ft)
     parity.check(name + " phi", ph, m.isochoric_array(3, T, rv), 0.0, rtol=5e-12)
     if lnphi and not name.startswith(("MIE", "GSAFT")):   # (the oracle's ln(phi) family is wired for GERG / cubic / PC-SAFT; phi covers the rest)
         # ln phi = grad/(RT) - ln Z: both parts are O(grad/RT), the difference can be arbitrarily small
         RT = m.get_R(x[:, 0]) * T
-        parity.check(name + " ln phi", lp, m.lnphi_family(0, T, rv), sg / RT)
+        parity.check(name + " ln phi", lp, m.lnphi_family(0, T, rv), sg / RT, ftol=2 * ft)   # device log vs glibc log in ln Z
 
 
 def isoprops(be, oracle, name, n=300):
@@ -369,7 +400,7 @@ def virials(be, oracle, name, n=200):
     spec, T, rho, x = cases.points(name, n)
     m = oracle.RefModel(spec)
     # rho = 0 is where the SAFT families' association / hard-sphere expressions are worst conditioned in BOTH implementations
-    rt = 1e-10 if name.startswith(("MIE", "GSAFT")) else 1e-12
+    rt = 1e-10 if name.startswith(("MIE", "GSAFT")) else (1e-11 if name.startswith("MF_") else 1e-12)
     for Nvir in (2, 3, 4):
         ref = [m.dmBnvirdTm(Nvir, k, T, x) for k in range(3)]
         for NT in range(3):
@@ -393,4 +424,23 @@ def sigma_derivs(be, oracle, name, n=200):
     fam = np.max(np.abs(ref) / np.array([1.0, 1.0, 2.0, 6.0, 24.0])[:, None], axis=0)
     fam = np.maximum(fam, extra_scale(name) * m.get_R(x[:, 0]) * T * rho)
     for k in range(5):
-        parity.check("%s Psir_sigma[%d]" % (name, k), got[k], ref[k], fam * parity.fact(k), ftol=5 * parity.FTOL)
+        parity.check("%s Psir_sigma[%d]" % (name, k), got[k], ref[k], fam * parity.fact(k), ftol=5 * ftol_for(name, 1))
+
+
+def ataudelta(be, oracle, name, n=100):
+    """get_AtaudeltaXi (derivs.hpp:341-351), all 23 combinations for every component, at tau = T_r(x)/T, delta = rho/rho_r(x) of the case's points"""
+    spec, T, rho, x = cases.points(name, n)
+    m = oracle.RefModel(spec)
+    nc = x.shape[0]
+    tau = np.array([m.reducing(0, x[:, k]) for k in range(n)]) / T
+    delta = rho / np.array([m.reducing(1, x[:, k]) for k in range(n)])
+    got = be.Ataudelta_table(spec, tau, delta, x)
+    ref = np.full(got.shape, np.nan)
+    for i in range(nc):
+        for (NT, ND, NX) in COMBOS_ATRHOXI:
+            ref[i, NT, ND, NX] = m.Ataudelta(1, NT, ND, (i, NX), tau, delta, x)
+        ref[i, 0, 0, 0] = m.Ar0n(1, T, rho, x)[0]
+    for (NT, ND, NX) in COMBOS_ATRHOXI:
+        S = parity.family_scale(ref[:, :NT + 1, :ND + 1, :NX + 1], (0, 1, 2, 3))
+        for i in range(nc):
+            parity.check("%s AtaudeltaXi NT%d ND%d X%d^%d" % (name, NT, ND, i, NX), got[i, NT, ND, NX], ref[i, NT, ND, NX], S, ftol=2 * ftol_for(name, ND) * 2**NX)

@@ -237,3 +237,26 @@ def test_cpp_abstractmodel_adapter():
     r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     print(r.stdout[-3000:])
     assert r.returncode == 0, r.stdout[-3000:]
+
+
+MF_CASES = ["MF_CH4_N2_O2", "MF_CH4_C2H6_CODATA", "MF_N2", "MF_R32_R125", "MF_NH3_AR"]
+
+
+@pytest.mark.parametrize("name", MF_CASES)
+def test_multifluid(be, oracle, name):
+    """the JSON-driven multifluid kind (multifluid.hpp:162-191, 948-995, 1095-1160; term types of multifluid_eosterms.hpp:
+    Power, Gaussian, Lemmon2005, GaoB, Exponential / GERG-2008 departure functions; mole-fraction-weighted and CODATA gas constants; the
+    single-component short circuit; the Lorentz-Berthelot estimate flag) through every entry point the GERG kinds are tested on"""
+    b = be
+    n = 300
+    ps.ar_tables(b, oracle, name, n=n)
+    ps.isochoric(b, oracle, name, n=n)
+    ps.virials(b, oracle, name, n=100)
+    ps.sigma_derivs(b, oracle, name, n=100)
+    if name != "MF_N2":
+        ps.atrhoxi(b, oracle, name, n=100)
+        ps.cross_composition(b, oracle, name, n=60)
+        ps.isoprops(b, oracle, name, n=100)
+        ps.ataudelta(b, oracle, name, n=100)
+    rows, bad = ps.truth_adjudication(b, oracle, name, n=300, what=("ar",))
+    assert not bad, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad]
