@@ -260,3 +260,18 @@ def test_multifluid(be, oracle, name):
         ps.ataudelta(b, oracle, name, n=100)
     rows, bad = ps.truth_adjudication(b, oracle, name, n=300, what=("ar",))
     assert not bad, [(r["output"], r["gpu_vs_truth_max"], r["oracle_vs_truth_max"]) for r in bad]
+
+
+def test_multifluid_coolprop_composition_derivative(be, oracle):
+    """the reference's documentation checks d(alphar)/dx_0 at constant tau, delta of methane + nitrogen + oxygen against CoolProp:
+    -0.0435874 (doc/source/derivs/compderivs.ipynb, cell 5; T = 300 K, rho = 3000 mol/m3, z = (0.3, 0.5, 0.2))"""
+    import cases
+    import numpy as np
+    b = be
+    spec = cases.SPECS["MF_CH4_N2_O2"][0]
+    m = oracle.RefModel(spec)
+    z = np.array([0.3, 0.5, 0.2])
+    tau = np.array([m.reducing(0, z) / 300.0]); delta = np.array([3000.0 / m.reducing(1, z)])
+    got = b.Ataudelta_table(spec, tau, delta, z[:, None].copy())[0, 0, 0, 1, 0]
+    assert abs(got - (-0.0435874)) < 5e-8
+    assert abs(got - m.Ataudelta(1, 0, 0, (0, 1), tau, delta, z[:, None].copy())[0]) < 1e-14
