@@ -21,7 +21,7 @@ SIGNIFICANT = 1e-2   # a value below this fraction of its family scale counts as
 REPORT = []   # (name, points, fraction needing the floor, max |d|/S, limit, fraction needing the floor among significant values)
 
 
-def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=0.02, ftol=FTOL):
+def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=0.02, ftol=FTOL, atol=0.0):
     got = np.asarray(got, dtype=np.float64); ref = np.asarray(ref, dtype=np.float64)
     assert got.shape == ref.shape, (name, got.shape, ref.shape)
     fin_r, fin_g = np.isfinite(ref), np.isfinite(got)
@@ -32,7 +32,7 @@ def check(name, got, ref, scale=None, rtol=RTOL, max_floor_frac=0.02, ftol=FTOL)
     d = np.where(fin_r, np.abs(got - ref), 0.0)
     a = np.where(fin_r, np.abs(ref), 1.0)
     s = np.where(np.isfinite(scale), scale, 0.0)
-    tol = rtol * a + ftol * s
+    tol = rtol * a + ftol * s + atol   # atol: only where an output contains a rounding of an O(1) intermediate (ln Z of Z = 1 + Ar01)
     bad = d > tol
     if np.any(bad):
         i = np.unravel_index(np.argmax(d / np.maximum(tol, 1e-300)), d.shape)
