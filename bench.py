@@ -119,6 +119,8 @@ def describe(wname, w, nc, total):
         call = "get_Arxy_batch[Ar00,01,02,10,11,20] + get_ln_fugacity_coefficients_batch"
     elif what == "ATrhoXi":
         call = "get_ATrhoXi_table_batch (23 combinations x %d components; 36 x %d rows written)" % (nc, nc)
+    elif what == "fgradHessian+dlnphi":
+        call = "build_Psir_fgradHessian_batch + isochoric_properties_batch[dlnphi_dT, dlnphi_drho, dlnphi_dx[%d]]" % (nc * nc)
     else:
         call = "build_Psir_fgradHessian_batch (Psir, grad[%d], Hessian[%d])" % (nc, nc * nc)
     fam = w["spec"]["kind"]
@@ -143,15 +145,23 @@ def make_steps(w, model, nc, n, xp):
         return (lambda mk: mk((nc, 3, 3, 4, n))), (lambda I, O: model.get_ATrhoXi_table_batch(I["T"], I["rho"], I["x"], out=O)), 36 * nc
     if what == "fgradHessian":
         return (lambda mk: (mk((1, n)), mk((nc, n)), mk((nc * nc, n)))), (lambda I, O: model.build_Psir_fgradHessian_batch(I["T"], I["rv"], out=O)), 1 + nc + nc * nc
+    if what == "fgradHessian+dlnphi":
+        # C5 as BASELINE.json words it: "isochoric Hessian/fugacity composition derivatives": Psir, gradient, Hessian AND d ln phi / dx (+ d/dT, d/drho)
+        which = ["dlnphi_dT", "dlnphi_drho", "dlnphi_dx"]
+
+        def step(I, O):
+            model.build_Psir_fgradHessian_batch(I["T"], I["rv"], out=O[:3])
+            model.isochoric_properties_batch(I["T"], I["rv"], which=which, out=dict(zip(which, O[3:])))
+        return (lambda mk: (mk((1, n)), mk((nc, n)), mk((nc * nc, n)), mk((nc, n)), mk((nc, n)), mk((nc * nc, n)))), step, 1 + 3 * nc + 2 * nc * nc
     raise SystemExit("unknown workload kind " + what)
 
 
 def needs_rv(w):
-    return w["what"] in ("Arxy+lnphi", "fgradHessian")
+    return w["what"] in ("Arxy+lnphi", "fgradHessian", "fgradHessian+dlnphi")
 
 
 def rows_in(w, nc):
-    return {"Ar0n": 2 + nc, "ATrhoXi": 2 + nc, "Arxy+lnphi": 2 + 2 * nc, "fgradHessian": 1 + nc}[w["what"]]
+    return {"Ar0n": 2 + nc, "ATrhoXi": 2 + nc, "Arxy+lnphi": 2 + 2 * nc, "fgradHessian": 1 + nc, "fgradHessian+dlnphi": 1 + nc}[w["what"]]
 
 
 def algorithmic_bytes(w, nc):
@@ -186,9 +196,15 @@ def cpu_reference_rate(wname, seconds):
                 for (a, b, c) in COMBOS_ATRHOXI:
                     out = m.ATrhoXi(a, b, i, c, T, rho, x)
             return out
+        if what == "fgradHessian+dlnphi":
+            rv = np.ascontiguousarray(x * rho)
+            m.fgradHessian(T, rv)
+            for q in (1, 2, 3):
+                out = m.lnphi_family(q, T, rv)
+            return out
         return m.fgradHessian(T, np.ascontiguousarray(x * rho))[0]
 
-    n0 = {"Ar0n": 4096, "Arxy+lnphi": 2048, "ATrhoXi": 16, "fgradHessian": 32}[what] * cores
+    n0 = {"Ar0n": 4096, "Arxy+lnphi": 2048, "ATrhoXi": 16, "fgradHessian": 32, "fgradHessian+dlnphi": 16}[what] * cores
     call(n0)  # warm-up, pages in the library
     t0 = time.perf_counter(); call(n0); dt = time.perf_counter() - t0
     rate = n0 / dt
@@ -369,7 +385,7 @@ def run_ours(args):
     if not args.no_e2e:
         if rank == 0:
             hin = {"T": teqp_b200.pinned_empty((Pe,))}
-            if w["what"] != "fgradHessian":
+            if not w["what"].startswith("fgradHessian"):
                 hin["rho"] = teqp_b200.pinned_empty((Pe,)); hin["x"] = teqp_b200.pinned_empty((nc, Pe))
             if needs_rv(w):
                 hin["rv"] = teqp_b200.pinned_empty((nc, Pe))
@@ -460,7 +476,7 @@ def run_ours(args):
         if world == 1 and wname == "C3" and not args.no_secondary:
             # the other BASELINE.json configs, device-resident, short (3 warm-up + 3 timed steps each): recorded by the driver with the headline
             sec = []
-            for name, npts2 in (("C1", 0), ("C1", 10**8), ("C2", 0), ("C4", 0), ("C5", 0)):
+            for name, npts2 in (("C1", 0), ("C1", 10**8), ("C2", 0), ("C4", 0), ("C5", 0), ("C5x", 0)):
                 try:
                     ww = WORKLOADS[name]
                     S = device_leg(name, npts2 or ww["npts"], 3, 3, False)

@@ -114,7 +114,12 @@ public:
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gerg_launch_ATrhoXi(P, in, out, st); }
     void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXj(P, in, i, j, out, st); }
     void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gergjet_launch_ATrhoXiXjXk(P, in, i, j, k, out, st); }
-    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { gergjet_launch_isoprops(P, in, o, st); }
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {
+        // analytic pass (tq_gerg_iso.cuh) where it applies; TEQPB200_GERG_ISOPROPS_JETS forces the jet sweeps (A/B and cross-check)
+        static const bool jets = std::getenv("TEQPB200_GERG_ISOPROPS_JETS") != nullptr;
+        if (!jets && src.all_plain_tau && !P.r_weighted && !P.pure_shortcut) gerg_launch_isoprops(P, Rgas, in, o, st);
+        else gergjet_launch_isoprops(P, in, o, st);
+    }
     // GERG200XReducing::get_Tr / get_rhor (GERG.hpp:179-205) on the host, same pair order and skip rule as the kernels
     bool reducing(const double* x, int n, double* Tr, double* rhor) const override {
         if (n != P.nc) throw InvalidArgument("mole fractions must be of size " + std::to_string(P.nc));

@@ -6,6 +6,20 @@ namespace tq {
 
 namespace {
 
+template<int WS>
+__global__ void __launch_bounds__(WS) gerg_isoprops_kernel(const __grid_constant__ GergProgram P, const double Rgas, const DeviceBatch in,
+                                                           const IsoPropsOut ip) {
+    extern __shared__ double Wsh[];
+    double* W = Wsh + threadIdx.x;
+    const long long k = (long long)blockIdx.x * WS + threadIdx.x;
+    if (k >= in.npts) return;
+    Exp2K K = Exp2K::load(in.npts >> 62);
+    K.load_thread((long long)(((unsigned)__double2hiint(__ldg(in.T + k)) >> 31) << 3));
+    for (int i = 0; i < P.nc; ++i) W[i * WS] = __ldg(in.x + (long long)i * in.x_stride + k);
+    const IsochoricOut none{};
+    gerg_iso_point<WS, true>(P, K, Rgas, __ldg(in.T + k), W, none, k, in.npts, &ip);
+}
+
 template<int WS, bool WANT_H>
 __global__ void __launch_bounds__(WS) gerg_isochoric_kernel(const __grid_constant__ GergProgram P, const double Rgas, const DeviceBatch in,
                                                             const IsochoricOut o) {
@@ -49,7 +63,23 @@ void launch_h(const GergProgram& P, double Rgas, const DeviceBatch& in, const Is
     else launch_ws<128, WANT_H>(P, Rgas, in, o, st, smem);
 }
 
+template<int WS>
+void launch_ip(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& ip, cudaStream_t st, size_t smem) {
+    auto kern = gerg_isoprops_kernel<WS>;
+    if (smem > 48 * 1024) TQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid_for(in.npts, WS, 1 << 30), WS, smem, st>>>(P, Rgas, in, ip);
+    TQ_CUDA(cudaGetLastError());
+}
+
 }  // namespace
+
+void gerg_launch_isoprops(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& ip, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const size_t rows = (size_t)gerg_iso_rows(P.nc, P.nw, true);
+    const size_t smem = rows * 32 * sizeof(double);
+    if (smem + 1024 > kSmemPerSM) throw InvalidArgument("mixture too large for the isochoric kernel's staging area");
+    launch_ip<32>(P, Rgas, in, ip, st, smem);
+}
 
 void gerg_launch_isochoric(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) {
     if (in.npts == 0) return;

@@ -44,9 +44,18 @@ TQ_HD GergPairD gerg_pair_first(double b2, double ri, double rj, double inv) {
     return r;
 }
 
+// The derived isochoric properties (IsoPropsOut; derivs.hpp:962-978, 1196-1201, 1264-1437, 1482-1494) come out of the same pass: with
+//   g_i = dPhi/drho_i,  P_i = d g_i / d ln tau = Phi_ss t_i + Phi_sr d_i + sum_w a_w,s w_i,  Q_i = Phi_sr t_i + Phi_rr d_i + sum_w a_w,r w_i
+// Euler's theorem for the scaling rhovec -> lambda rhovec (x, tau fixed; delta -> lambda delta) gives (H rhovec)_i = RT Q_i, so nothing has to
+// be accumulated over the Hessian rows:
+//   d2Psir/dT drho_i = R (g_i - P_i)                       dp/drho_i = RT (1 + Q_i)             v_i = (1 + Q_i) / (rho (1 + 2 Ar01 + Ar02))
+//   d ln phi_i / dT  = -P_i / T + Ar11 / (T Z)             d ln phi_i / drho = (Q_i - (Ar01 + Ar02) / Z) / rho
+//   d ln phi_i / dx_j = rho H_ij / RT - (dZ/dx_j) / Z,     dZ/dx_j = rho d2 alphar / drho dx_j = Q_j + sum_q a_q,r w_q / rho + (2 Phi_sr + Phi_rr) / rho
+//   p_r = RT Phi_r,  s+ = (Phi - Phi_s) / rho,  dp/dT = R (rho + Phi_r - Phi_sr)
+// (the reference forms the full Hessian by Nc (Nc + 1) / 2 second-order sweeps and multiplies it by a vector for each of these).
 template<int WS, bool WANT_H>
 TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rgas, const double T, double* W, const IsochoricOut& o,
-                          const long long k, const long long npts) {
+                          const long long k, const long long npts, const IsoPropsOut* ipp = nullptr) {
     constexpr int SH = (WS == 128) ? 0 : (WS == 64) ? 1 : (WS == 32) ? 2 : (WS == 16) ? 3 : (WS == 8) ? 4 : (WS == 4) ? 5 : (WS == 2) ? 6 : 7;
     static_assert((kGergWS >> SH) == WS, "WS must be a power of two <= kGergWS");
     constexpr int NO = WANT_H ? 2 : 1;  // order of the total-derivative table
@@ -257,6 +266,16 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         }
     }
     if (!WANT_H) return;
+    const bool want_ip = ipp != nullptr;
+    const double Z = 1.0 + Fr * invr;
+    const double Ar02 = 2.0 * A[0][NO] * invr, Ar11 = Fsr * invr;
+    const double dZx0 = Srr + (2.0 * Fsr + Frr) * invr;   // dZ/dx_j = Q_j + dZx0
+    if (want_ip) {
+        const IsoPropsOut& ip = *ipp;
+        if (ip.pr) ip.pr[k] = RT * Fr;
+        if (ip.splus) ip.splus[k] = (A[0][0] - Fs) * invr;
+        if (ip.dpdT) ip.dpdT[k] = Rgas * (rhotot + Fr - Fsr);
+    }
 
     // ---- E_k = -(1/rho^2) sum_{q contains k} M_q rho_other, into the rows the departure weights no longer need -------------
     for (int i = 0; i < nc; ++i) Eref(i) = 0.0;
@@ -279,6 +298,22 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         const double ti = gTi - 2.0 * invr, di = gVi - invr;
         const double csi = as[i * WS], cri = ar[i * WS], Ei = Eref(i);
         const double Pi = fma(Fss, ti, fma(Fsr, di, csi)), Qi = fma(Fsr, ti, fma(Frr, di, cri));
+        if (want_ip) {
+            const IsoPropsOut& ip = *ipp;
+            const double gi = fma(Fs, ti, fma(Fr, di, aw[i * WS] - S0r));
+            const long long oi = (long long)i * npts + k;
+            const double R1 = Rgas * (1.0 + log(ri));   // R (rho_ref + ln(rho_i / rho_ref)), rho_ref = 1 (derivs.hpp:1201, 1414)
+            if (ip.d2PsirdTdrhoi) ip.d2PsirdTdrhoi[oi] = Rgas * (gi - Pi);
+            if (ip.dpdrhovec) ip.dpdrhovec[oi] = fma(RT, Qi, RT);
+            if (ip.pmv) ip.pmv[oi] = (1.0 + Qi) / (rhotot * (1.0 + 2.0 * Fr * invr + Ar02));
+            if (ip.chempotVLE) ip.chempotVLE[oi] = fma(RT, gi, T * R1);
+            if (ip.dchempotdT) ip.dchempotdT[oi] = Rgas * (gi - Pi) + R1;
+            if (ip.dlnphi_dT) ip.dlnphi_dT[oi] = (Ar11 / Z - Pi) / T;
+            const double dr = (Qi - (Fr * invr + Ar02) / Z) * invr;
+            if (ip.dlnphi_drho) ip.dlnphi_drho[oi] = dr;
+            if (ip.dlnphi_dv) ip.dlnphi_dv[oi] = -dr * (rhotot * rhotot);
+        }
+        const double dZxi = Qi + dZx0;
         double hdi = hd[i * WS];
         for (int j = i + 1; j < nc; ++j, ++pidx) {
             const double rj = W[j * WS];
@@ -305,16 +340,24 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
             h = fma(Fr, fma(-gVi, gVj, yV), h);
             h += Ei + Eref(j) + const0;
             if (qn < ndep && P.dep_i[qn] == i && P.dep_j[qn] == j) { h = fma(aw[(nc + qn) * WS], invr, h); ++qn; }
+            if (want_ip && ipp->dlnphi_dx) {
+                const double Qj = fma(Fsr, tj, fma(Frr, dj, ar[j * WS]));
+                ipp->dlnphi_dx[(ncl * i + j) * npts + k] = fma(rhotot, h, -(Qj + dZx0) / Z);   // d ln phi_i / d x_j
+                ipp->dlnphi_dx[(ncl * j + i) * npts + k] = fma(rhotot, h, -dZxi / Z);          // d ln phi_j / d x_i
+            }
             h *= RT;
-            o.hess[(ncl * i + j) * npts + k] = h;
-            o.hess[(ncl * j + i) * npts + k] = h;
+            if (o.hess) {
+                o.hess[(ncl * i + j) * npts + k] = h;
+                o.hess[(ncl * j + i) * npts + k] = h;
+            }
         }
         {
             double h = fma(ti, Pi, fma(di, Qi, fma(ti, csi, di * cri)));
             h = fma(-Fs * gTi, gTi, h);
             h = fma(-Fr * gVi, gVi, h);
             h += hdi + 2.0 * Ei + const0;
-            o.hess[(ncl * i + i) * npts + k] = RT * h;
+            if (want_ip && ipp->dlnphi_dx) ipp->dlnphi_dx[(ncl * i + i) * npts + k] = fma(rhotot, h, -dZxi / Z);
+            if (o.hess) o.hess[(ncl * i + i) * npts + k] = RT * h;
         }
     }
 }
@@ -323,5 +366,7 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
 void gerg_launch_ATrhoXi(const GergProgram& P, const DeviceBatch& in, double* out, cudaStream_t st);
 // host launcher (tq_gerg_iso.cu)
 void gerg_launch_isochoric(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st);
+// the derived isochoric properties from the same analytic pass (tau^t temperature shapes, constant R)
+void gerg_launch_isoprops(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st);
 
 }  // namespace tq

@@ -144,7 +144,7 @@ class Model:
 
     ISOPROPS = ["pr", "splus", "dpdT", "d2PsirdTdrhoi", "dpdrhovec", "pmv", "chempotVLE", "dchempotdT", "dlnphi_dT", "dlnphi_drho", "dlnphi_dv", "dlnphi_dx"]
 
-    def isochoric_properties_batch(self, T, rhovec, which=None):
+    def isochoric_properties_batch(self, T, rhovec, which=None, out=None):
         """dict of derived isochoric properties (names: Model.ISOPROPS; teqpcpp.hpp:52-75, 128-160), one launch"""
         which = list(self.ISOPROPS) if which is None else list(which)
         dev = _is_torch(T)
@@ -153,7 +153,7 @@ class Model:
         nc = rhovec.shape[0]
         aT, av = _Arg(T, dev), _Arg(rhovec, dev)
         rows = dict(zip(self.ISOPROPS, [1, 1, 1] + [nc] * 8 + [nc * nc]))
-        outs = {k: _Arg(self._out((rows[k], n), dev, T), dev) for k in which}
+        outs = {k: _Arg(self._out((rows[k], n), dev, T, None if out is None else out.get(k)), dev) for k in which}
         null = C.POINTER(C.c_double)()
         ptrs = [outs[k].ptr if k in outs else null for k in self.ISOPROPS]
         err = C.create_string_buffer(2000)

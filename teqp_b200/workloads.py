@@ -94,6 +94,8 @@ WORKLOADS = {
                T=(250.0, 450.0), rho=(10.0, 25000.0), z0=_norm(_C5_Z), npts=10**6, npts_strong=8 * 10**6, what="fgradHessian", nmax=4,
                bytes_per_point=8 * 22 + 8 * (1 + 21 + 441)),
 }
+# C5 with the fugacity composition derivatives in the same step (BASELINE.json configs[4] names both)
+WORKLOADS["C5x"] = dict(WORKLOADS["C5"], what="fgradHessian+dlnphi", bytes_per_point=8 * 22 + 8 * (1 + 3 * 21 + 2 * 441))
 
 
 def workload_points(name, npts, k0=0):

@@ -114,6 +114,16 @@ void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const doub
         else gerg_iso_point<WS, false>(P, K, Rgas, T[k], W.data(), o, k, npts);
     }
 }
+void gerg_ip_loop(const GergProgram& P, double Rgas, long long npts, const double* T, const double* rv, const IsoPropsOut& ip) {
+    constexpr int WS = 32;
+    const Exp2K K = Exp2K::load();
+    std::vector<double> W((size_t)gerg_iso_rows(P.nc, P.nw, true) * WS);
+    const IsochoricOut none{};
+    for (long long k = 0; k < npts; ++k) {
+        for (int i = 0; i < P.nc; ++i) W[(size_t)i * WS] = rv[(long long)i * npts + k];
+        gerg_iso_point<WS, true>(P, K, Rgas, T[k], W.data(), none, k, npts, &ip);
+    }
+}
 // cross-composition tables: which = 2 -> (i, j) table [36][npts]; which = 3 -> (i, j, k) table [32][npts]
 template<class M>
 void generic_xx(const typename M::Params& p, int nc, int which, int i, int j, int k, long long npts, const double* T, const double* rho, const double* x, double* out) {
@@ -264,7 +274,12 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         o.chempotVLE = outs[6]; o.dchempotdT = outs[7]; o.dlnphi_dT = outs[8]; o.dlnphi_drho = outs[9]; o.dlnphi_dv = outs[10]; o.dlnphi_dx = outs[11];
         if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
-        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_ip<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
+            const GergProgram& P = *static_cast<const GergProgram*>(blob);
+            // same dispatch as GergModel::launch_isoprops
+            if (P.ntf == 0 && !P.r_weighted && !P.pure_shortcut && !std::getenv("TEQPB200_GERG_ISOPROPS_JETS")) gerg_ip_loop(P, P.Rgas, npts, T, rhovec, o);
+            else generic_ip<GergJetDev>(P, ncomp, npts, T, rhovec, o);
+        }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
