@@ -10,6 +10,7 @@
 //             = rho                                                                      (van der Waals)
 #pragma once
 #include "tq_jet.cuh"
+#include "tq_math.cuh"
 
 namespace tq {
 
@@ -104,8 +105,10 @@ TQ_HD void cubic_table_point(const CubicParams& p, const double T, const double 
 
     // the m = 0 values follow the reference's operation order (simple_cubics.hpp:250-253): at low density -ln(1-b rho) and the
     // Psi_plus logarithm amplify a 1-ulp difference in their arguments by 1/(b rho)
+    // Only the m = 0 entries keep IEEE divisions; the ratios that feed the m >= 1 closed forms use a Newton-refined reciprocal (no
+    // slow-path guards: 1 - y, n1, n2 and b (Delta1 - Delta2) are O(1) and away from zero for every physical state)
     const double y = b * rho;
-    const double u = y / (1.0 - y);
+    const double u = y * fast_rcp(1.0 - y);
     double v1 = 0.0, v2 = 0.0, invbd = 0.0;
     double psi_m = -log(1.0 - y);
     double psi_p;
@@ -114,10 +117,10 @@ TQ_HD void cubic_table_point(const CubicParams& p, const double T, const double 
     } else {
         const double n1 = p.Delta1 * b * rho + 1.0, n2 = p.Delta2 * b * rho + 1.0;
         const double bd = b * (p.Delta1 - p.Delta2);
-        invbd = 1.0 / bd;
+        invbd = fast_rcp(bd);
         psi_p = log(n1 / n2) / bd;
-        v1 = p.Delta1 * y / n1;
-        v2 = p.Delta2 * y / n2;
+        v1 = p.Delta1 * y * fast_rcp(n1);
+        v2 = p.Delta2 * y * fast_rcp(n2);
     }
     double um = 1.0, v1m = 1.0, v2m = 1.0, fact = 1.0;  // fact = (m-1)!
     for (int m = 0; m <= ND; ++m) {

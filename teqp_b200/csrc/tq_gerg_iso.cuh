@@ -26,7 +26,14 @@
 #include "tq_common.hpp"
 #include "tq_gerg.cuh"
 
+#ifndef TQ_ISO_UNROLL
+#define TQ_ISO_UNROLL 1   // unroll factor of the pair loops of passes A and C.  Measured on B200 (profiles/r02g, C5 10^6 points): 1 -> 120.5,
+                          // 2 -> 123.5, 4 -> 121.7 Mpt/s: the loop bodies branch (zero denominators, beta = 1 pairs), so unrolling does not
+                          // interleave iterations; one warp per scheduler stays latency-bound
+#endif
+
 namespace tq {
+constexpr int kIsoUnroll = TQ_ISO_UNROLL;
 
 // rows of the staging area.  Hessian path: weights, three per-weight arrays, the Nc-vectors dlnY_T, dlnY_V and the running diagonal
 // sums; the vector E lives in rows that are free once the departure weights have been reduced (2 ndep of them), plus nc - 2 ndep
@@ -88,9 +95,23 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         for (int i = 0; i < nc; ++i) {
             const double ri = W[i * WS];
             double gTi = 0.0, gVi = 0.0;
+#pragma unroll kIsoUnroll
             for (int j = i + 1; j < nc; ++j, ++pidx) {
                 const double rj = W[j * WS];
                 const GergRedPair pr = P.pair[pidx];
+                if (pr.beta2T == 1.0 && pr.beta2V == 1.0) {
+                    // beta_T = beta_v = 1 (154 of the 210 GERG-2008 pairs): the pair term ri rj (ri + rj) / (ri + rj) is ri rj -- gradient
+                    // (rj, ri), mixed second derivative 1, no diagonal part.  The branch is uniform over the warp (same pair for every thread).
+                    if (ri + rj == 0.0) continue;
+                    const double pij = ri * rj;
+                    YT = fma(pr.YT2, pij, YT);
+                    YV = fma(pr.YV2, pij, YV);
+                    gTi = fma(pr.YT2, rj, gTi);
+                    gVi = fma(pr.YV2, rj, gVi);
+                    vt[j * WS] = fma(pr.YT2, ri, vt[j * WS]);
+                    vd[j * WS] = fma(pr.YV2, ri, vd[j * WS]);
+                    continue;
+                }
                 const double dT = fma(pr.beta2T, ri, rj), dV = fma(pr.beta2V, ri, rj);
                 const double den = dT * dV;
                 if (den == 0.0) continue;  // both concentrations zero: the reference skips the pair (GERG.hpp:189)
@@ -315,13 +336,16 @@ TQ_HD void gerg_iso_point(const GergProgram& P, const Exp2K& K, const double Rga
         }
         const double dZxi = Qi + dZx0;
         double hdi = hd[i * WS];
+#pragma unroll kIsoUnroll
         for (int j = i + 1; j < nc; ++j, ++pidx) {
             const double rj = W[j * WS];
             const GergRedPair pr = P.pair[pidx];
             const double dT = fma(pr.beta2T, ri, rj), dV = fma(pr.beta2V, ri, rj);
             const double den = dT * dV;
             double yT = 0.0, yV = 0.0;  // Y_ij / Y
-            if (den != 0.0) {
+            if (pr.beta2T == 1.0 && pr.beta2V == 1.0) {
+                if (den != 0.0) { yT = pr.YT2 * iYT; yV = pr.YV2 * iYV; }
+            } else if (den != 0.0) {
                 const double inv = fast_rcp(den);
                 const double invT = inv * dV, invV = inv * dT;
                 const GergPairD a = gerg_pair_first(pr.beta2T, ri, rj, invT);

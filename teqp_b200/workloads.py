@@ -80,7 +80,7 @@ def _norm(z):
 WORKLOADS = {
     # C1: Peng-Robinson pure methane (values of src/tests/catch_test_cubics.cxx:28-30), Ar00..Ar04
     "C1": dict(spec={"kind": "PR", "model": {"Tcrit / K": [190.564], "pcrit / Pa": [4599200], "acentric": [0.011]}},
-               T=(100.0, 600.0), rho=(1.0, 25000.0), z0=[1.0], npts=10**6, what="Ar0n", nmax=4, bytes_per_point=56, bound="hbm"),
+               T=(100.0, 600.0), rho=(1.0, 25000.0), z0=[1.0], npts=10**6, what="Ar0n", nmax=4, bytes_per_point=56, bound="hbm", x_broadcast=True),
     # C2: PC-SAFT methane + ethane (library values, include/teqp/models/pcsaft.hpp:53-54)
     "C2": dict(spec={"kind": "PCSAFT", "model": {"names": ["Methane", "Ethane"]}},
                T=(150.0, 450.0), rho=(1.0, 20000.0), z0=[0.5, 0.5], npts=10**7, what="Arxy+lnphi", bytes_per_point=96),
