@@ -61,7 +61,9 @@ int get_Ar0n_batch(const long long int uuid, const int nmax, const long long int
 /* AbstractModel::get_Ar{nmax}0n (teqpcpp.hpp:115-117; derivs.hpp:571-611): out[n][k] = (1/T)^n d^n alphar/d(1/T)^n, n = 0..nmax (nmax 0..4) */
 int get_Arn0_batch(const long long int uuid, const int nmax, const long long int npts, const double* T, const double* rho,
                    const double* molefrac, const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
-/* AbstractModel::get_Arxy for several (NT[p], ND[p]) at once (teqpcpp.hpp:104-109; derivs.hpp:150-238): out[p][k] */
+/* AbstractModel::get_Arxy for several (NT[p], ND[p]) at once (teqpcpp.hpp:104-109; derivs.hpp:150-238): out[p][k].  Reachable pairs, the same
+   for every model family: NT = 0 with ND <= 6; ND = 0 with NT <= 4; NT <= 2 with ND <= 4 (a superset of the reference's runtime dispatch,
+   NT + ND <= 3).  The pairs are partitioned over at most three sweeps (density row, temperature column, mixed block), each run once. */
 int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, const int* ND, const long long int npts,
                    const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out,
                    const int flags, char* errmsg, int errmsg_length);

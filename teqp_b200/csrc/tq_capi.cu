@@ -522,20 +522,50 @@ int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, co
         auto m = lookup(uuid);
         check_ncomp(*m, Ncomp);
         if (npairs <= 0) throw InvalidArgument("npairs must be positive");
-        int NTm = 0, NDm = 0;
+        // The requested pairs are partitioned over the sweeps every family compiles: the density row (NT = 0, ND <= 6), the temperature
+        // column (ND = 0, NT <= 4) and the mixed block (NT <= 2, ND <= 4); each needed sweep runs once, sized by the largest order asked
+        // of it.  Pairs outside all three (NT >= 3 with ND >= 1, or NT >= 1 with ND >= 5) are rejected -- the reference's own runtime
+        // dispatch serves NT + ND <= 3 only (derivs.hpp:627-682), all of which are covered.
+        int rowND = -1, colNT = -1, blkNT = -1, blkND = -1;
+        std::vector<int> where(npairs);   // 0: row, 1: column, 2: block
         for (int p = 0; p < npairs; ++p) {
-            if (NT[p] < 0 || ND[p] < 0 || NT[p] > kMaxDerivT || ND[p] > kMaxDerivD) throw InvalidArgument("derivative order out of range");
-            NTm = std::max(NTm, NT[p]); NDm = std::max(NDm, ND[p]);
+            const int nt = NT[p], nd = ND[p];
+            if (nt < 0 || nd < 0 || nt > kMaxDerivT || nd > kMaxDerivD) throw InvalidArgument("derivative order out of range");
+            if (nt == 0) { where[p] = 0; rowND = std::max(rowND, nd); }
+            else if (nd == 0) { where[p] = 1; colNT = std::max(colNT, nt); }
+            else if (nt <= 2 && nd <= 4) { where[p] = 2; blkNT = std::max(blkNT, nt); blkND = std::max(blkND, nd); }
+            else throw InvalidArgument("mixed derivative (" + std::to_string(nt) + "," + std::to_string(nd) + ") is outside the compiled sweeps: NT = 0 with ND <= 6, ND = 0 with NT <= 4, or NT <= 2 with ND <= 4");
+        }
+        // a pair of the row / column that the block sweep covers anyway rides along with it
+        if (blkNT >= 0) {
+            bool row_needed = false, col_needed = false;
+            for (int p = 0; p < npairs; ++p) {
+                if (where[p] == 0 && ND[p] > blkND) row_needed = true;
+                if (where[p] == 1 && NT[p] > blkNT) col_needed = true;
+            }
+            for (int p = 0; p < npairs; ++p) {
+                if (where[p] == 0 && !row_needed) where[p] = 2;
+                if (where[p] == 1 && !col_needed) where[p] = 2;
+            }
+            if (!row_needed) rowND = -1;
+            if (!col_needed) colNT = -1;
         }
         const bool bc = flags & TEQPB200_BROADCAST_X;
-        const int rows = (NTm + 1) * (NDm + 1);
-        // one sweep computes the covering table; the requested rows are then gathered
-        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, npairs}, {nullptr, rows}},
+        const int rows_row = rowND >= 0 ? rowND + 1 : 0, rows_col = colNT >= 0 ? colNT + 1 : 0, rows_blk = blkNT >= 0 ? (blkNT + 1) * (blkND + 1) : 0;
+        run(flags, npts, {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}}, {{out, npairs}, {nullptr, rows_row + rows_col + rows_blk}},
             [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
-                m->launch_ar_table(NTm, NDm, make_batch(n, din[0], din[1], din[2], bc), dout[1], st);
-                ++g_launches;
-                for (int p = 0; p < npairs; ++p)
-                    TQ_CUDA(cudaMemcpyAsync(dout[0] + (size_t)p * n, dout[1] + (size_t)(NT[p] * (NDm + 1) + ND[p]) * n, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+                const DeviceBatch b = make_batch(n, din[0], din[1], din[2], bc);
+                double* srow = dout[1];
+                double* scol = srow + (size_t)rows_row * n;
+                double* sblk = scol + (size_t)rows_col * n;
+                if (rows_row) { m->launch_ar_table(0, rowND, b, srow, st); ++g_launches; }
+                if (rows_col) { m->launch_ar_table(colNT, 0, b, scol, st); ++g_launches; }
+                if (rows_blk) { m->launch_ar_table(blkNT, blkND, b, sblk, st); ++g_launches; }
+                for (int p = 0; p < npairs; ++p) {
+                    const double* src = where[p] == 0 ? srow + (size_t)ND[p] * n : where[p] == 1 ? scol + (size_t)NT[p] * n
+                                                                                                 : sblk + (size_t)(NT[p] * (blkND + 1) + ND[p]) * n;
+                    TQ_CUDA(cudaMemcpyAsync(dout[0] + (size_t)p * n, src, sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
+                }
             });
     });
 }

@@ -275,3 +275,27 @@ def test_multifluid_coolprop_composition_derivative(be, oracle):
     got = b.Ataudelta_table(spec, tau, delta, z[:, None].copy())[0, 0, 0, 1, 0]
     assert abs(got - (-0.0435874)) < 5e-8
     assert abs(got - m.Ataudelta(1, 0, 0, (0, 1), tau, delta, z[:, None].copy())[0]) < 1e-14
+
+
+@pytest.mark.parametrize("name", ["PR2k", "PCSAFT2", "GERG10", "MIE3", "MF_CH4_N2_O2"])
+def test_arxy_batch_mixed_axis_pair_lists(be, oracle, name):
+    """get_Arxy_batch partitions the requested pairs over the compiled sweeps (density row, temperature column, mixed block): pair lists that
+    span several of them -- [(3,0),(0,3)], [(0,6),(2,0)], [(4,0),(1,4),(0,5)] -- are served for every family and equal the single-sweep
+    tables; pairs outside every sweep are rejected with a message, identically for every family"""
+    import teqp_b200
+    spec, T, rho, x = cases.points(name, 500)
+    m = be.model(spec)
+    t06 = m.get_Ar0n_batch(6, T, rho, x); t40 = m.get_Arn0_batch(4, T, rho, x)
+    blk_pairs = [(i, j) for i in range(3) for j in range(5)]
+    blk = m.get_Arxy_batch(blk_pairs, T, rho, x).reshape(3, 5, -1)
+    for pairs in ([(3, 0), (0, 3)], [(0, 6), (2, 0)], [(4, 0), (1, 4), (0, 5)], [(0, 0)], [(1, 1), (0, 2), (2, 0)]):
+        got = m.get_Arxy_batch(pairs, T, rho, x)
+        for q, (nt, nd) in enumerate(pairs):
+            want = t06[nd] if nt == 0 and nd > 4 else t40[nt] if nd == 0 and nt > 2 else blk[nt, nd]
+            ref = t06[nd] if nt == 0 else t40[nt] if nd == 0 else blk[nt, nd]
+            # different sweeps may serve the same entry: equal to the parity rule's floor, not bit for bit
+            fam = np.maximum(np.abs(ref), parity.coeff_scale(t06[None]) * parity.fact(nt, nd))
+            parity.check("%s Arxy_batch (%d,%d)" % (name, nt, nd), got[q], ref, fam, ftol=max(ps.ftol_for(name, nd), 1e-13))
+    for bad in ([(3, 1)], [(1, 5)], [(0, 7)], [(5, 0)]):
+        with pytest.raises(teqp_b200.TeqpError):
+            m.get_Arxy_batch(bad, T, rho, x)
