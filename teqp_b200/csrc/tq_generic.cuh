@@ -510,6 +510,114 @@ void generic_launch_isoprops(const typename M::Params& p, int nc, const DeviceBa
 
 
 // ------------------------------------------------------------------------------------------------------------------
+// The same derived properties as THREE kernels with ONE jet shape each, for families whose model code is too large for NVVM to compile
+// all seven instantiations into one kernel (SAFT-VR-Mie + association): each lives in its own translation unit.
+//   part L  (J3<1,2,0>): Lambda_nm (n <= 1, m <= 2) -> pr, splus, and the six numbers into scratch L[6][npts]
+//   part C  (J3<1,1,1>): per component gradient, d/dT of the gradient and the Hessian-vector product H rhovec -> every vector output, dp/dT
+//   part X  (J3<0,1,1>): dZ/dx_j, combined with the Hessian the isochoric kernel wrote to scratch H[nc*nc][npts] -> d ln phi_i / d x_j
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN>
+TQ_HD void generic_ip_L_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const IsoPropsOut& o, double* Ls,
+                              const long long k, const long long npts) {
+    double rhotot = 0.0;
+    for (int i = 0; i < nc; ++i) rhotot += rv[i];
+    using X0 = J3<0, 0, 0>;
+    X0 x[MAXN];
+    for (int i = 0; i < nc; ++i) x[i] = X0(rv[i] / rhotot);
+    const double R = base(M::R(p, x));
+    const J3<1, 0, 0> T = J3<1, 0, 0>::reciprocal_scaled_variable(T0);
+    J3<0, 2, 0> rho;
+    rho.c[0] = Tay<2, Tay<0, double>>::scaled_variable(rhotot);
+    const J3<1, 2, 0> a = embed<J3<1, 2, 0>>(M::template alphar<MAXN>(p, T, rho, x));
+    double L[2][3];
+    for (int n = 0; n < 2; ++n)
+        for (int m = 0; m < 3; ++m) { L[n][m] = (m == 2 ? 2.0 : 1.0) * a.c[n].c[m].c[0]; Ls[(long long)(n * 3 + m) * npts + k] = L[n][m]; }
+    if (o.pr) o.pr[k] = L[0][1] * rhotot * R * T0;
+    if (o.splus) o.splus[k] = L[0][0] - L[1][0];
+}
+
+template<class M, int MAXN>
+TQ_HD void generic_ip_C_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const IsoPropsOut& o, const double* Ls,
+                              const long long k, const long long npts) {
+    double rhotot = 0.0;
+    for (int i = 0; i < nc; ++i) rhotot += rv[i];
+    using X0 = J3<0, 0, 0>;
+    X0 x[MAXN];
+    for (int i = 0; i < nc; ++i) x[i] = X0(rv[i] / rhotot);
+    const double R = base(M::R(p, x));
+    const double RT = R * T0;
+    const double L01 = Ls[1 * npts + k], L02 = Ls[2 * npts + k], L11 = Ls[4 * npts + k];
+    const double Z = 1.0 + L01;
+    const double dZdrho = (L01 + L02) / rhotot;
+    const double dZdT_Z = L11 / (-T0) / Z;
+    double dPsirdT = 0.0, dot_Tgrad = 0.0;
+    for (int i = 0; i < nc; ++i) {
+        const J3<1, 1, 1> d = psir_dir_jet<M, MAXN, 1, 1, 1>(p, nc, T0, rv, i, rv);
+        const double grad = d.c[0].c[1].c[0], Tgrad = d.c[1].c[1].c[0], Hrho = d.c[0].c[1].c[1];
+        dPsirdT = d.c[1].c[0].c[0];
+        dot_Tgrad += rv[i] * Tgrad;
+        const long long q = (long long)i * npts + k;
+        const double dpdrho_i = RT + Hrho;
+        if (o.d2PsirdTdrhoi) o.d2PsirdTdrhoi[q] = Tgrad;
+        if (o.dpdrhovec) o.dpdrhovec[q] = dpdrho_i;
+        if (o.pmv) o.pmv[q] = (-rhotot * dpdrho_i) / (-(rhotot * rhotot) * RT * (1.0 + 2.0 * L01 + L02));
+        if (o.chempotVLE) o.chempotVLE[q] = grad + RT * (1.0 + log(rv[i]));
+        if (o.dchempotdT) o.dchempotdT[q] = Tgrad + R * (1.0 + log(rv[i]));
+        if (o.dlnphi_dT) o.dlnphi_dT[q] = 1.0 / RT * (Tgrad - 1.0 / T0 * grad) - dZdT_Z;
+        const double dlr = 1.0 / RT * (Hrho / rhotot) - dZdrho / Z;
+        if (o.dlnphi_drho) o.dlnphi_drho[q] = dlr;
+        if (o.dlnphi_dv) o.dlnphi_dv[q] = dlr * (-(rhotot * rhotot));
+    }
+    if (o.dpdT) o.dpdT[k] = rhotot * R - dPsirdT + dot_Tgrad;
+}
+
+template<class M, int MAXN>
+TQ_HD void generic_ip_X_point(const typename M::Params& p, const int nc, const double T0, const double* rv, const IsoPropsOut& o, const double* Ls,
+                              const double* H, const long long k, const long long npts) {
+    double rhotot = 0.0;
+    for (int i = 0; i < nc; ++i) rhotot += rv[i];
+    using X0 = J3<0, 0, 0>;
+    X0 x0[MAXN];
+    for (int i = 0; i < nc; ++i) x0[i] = X0(rv[i] / rhotot);
+    const double RT = base(M::R(p, x0)) * T0;
+    const double Z = 1.0 + Ls[1 * npts + k];
+    const double f = rhotot / RT;
+    for (int j = 0; j < nc; ++j) {
+        using XT = J3<0, 0, 1>;
+        XT xj[MAXN];
+        for (int c = 0; c < nc; ++c) { xj[c] = XT(rv[c] / rhotot); if (c == j) xj[c].c[0].c[0].c[1] = 1.0; }
+        J3<0, 1, 0> rho;
+        rho.c[0] = Tay<1, Tay<0, double>>::scaled_variable(rhotot);
+        const J3<0, 1, 1> a = embed<J3<0, 1, 1>>(M::template alphar<MAXN>(p, J3<0, 0, 0>(T0), rho, xj));
+        const double dZdx_Z = a.c[0].c[1].c[1] / Z;
+        for (int i = 0; i < nc; ++i) o.dlnphi_dx[(long long)(i * nc + j) * npts + k] = f * H[(long long)(i * nc + j) * npts + k] - dZdx_Z;
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int PART>
+__global__ void __launch_bounds__(64) generic_ip_part_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                             const IsoPropsOut o, double* __restrict__ Ls, const double* __restrict__ H) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double rv[M::kMaxC];
+        for (int i = 0; i < nc; ++i) rv[i] = __ldg(in.x + (long long)i * in.x_stride + k);
+        if constexpr (PART == 0) generic_ip_L_point<M, M::kMaxC>(p, nc, __ldg(in.T + k), rv, o, Ls, k, npts);
+        else if constexpr (PART == 1) generic_ip_C_point<M, M::kMaxC>(p, nc, __ldg(in.T + k), rv, o, Ls, k, npts);
+        else generic_ip_X_point<M, M::kMaxC>(p, nc, __ldg(in.T + k), rv, o, Ls, H, k, npts);
+    }
+}
+template<class M, int PART>
+void generic_launch_ip_part(const typename M::Params& p, int nc, const DeviceBatch& in, const IsoPropsOut& o, double* Ls, const double* H, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    generic_ip_part_kernel<M, PART><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, o, Ls, H);
+    TQ_CUDA(cudaGetLastError());
+}
+#endif  // __CUDACC__
+
+// ------------------------------------------------------------------------------------------------------------------
 // get_Psir_sigma_derivs (derivs.hpp:1496-1509): Psi^r(T, rhovec + sigma v) to fourth order in sigma, one Tay<4> sweep
 // (the reference uses autodiff::Real<4> the same way): out[k][npts] = d^k Psir / dsigma^k, k = 0..4
 // ------------------------------------------------------------------------------------------------------------------

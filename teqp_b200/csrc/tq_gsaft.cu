@@ -20,7 +20,12 @@ void gsaft_launch_ar_rho(const GsaftParams&, int ND, const DeviceBatch&, double*
 void gsaft_launch_ar_mixed(const GsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_ATrhoXi(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_isochoric(const GsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void gsaft_launch_cross2(const GsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);   // tq_xx_gsaft_{2,3}.cu (directional jets)
+void gsaft_launch_cross3(const GsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 void gsaft_launch_sigma(const GsaftParams&, const DeviceBatch&, const double*, double*, cudaStream_t);   // tq_ex_gsaft.cu
+void gsaft_launch_ip_part0(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);   // tq_ip_gsaft_{L,C,X}.cu
+void gsaft_launch_ip_part1(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
+void gsaft_launch_ip_part2(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
 
 namespace {
 
@@ -56,8 +61,28 @@ public:
     }
     void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { launch_ar_table(NT, ND, in, out, st); }
     void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { gsaft_launch_sigma(p, in, v, out, st); }
+    void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gsaft_launch_cross2(p, in, i, j, -1, out, st); }
+    void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gsaft_launch_cross3(p, in, i, j, k, out, st); }
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gsaft_launch_ATrhoXi(p, in, out, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { gsaft_launch_isochoric(p, in, o, st); }
+    // derived isochoric properties: three single-shape kernels + the Hessian of the isochoric kernel (scratch on the stream)
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {
+        if (in.npts == 0) return;
+        const int nc = p.mie.nc;
+        double *Ls = nullptr, *H = nullptr;
+        TQ_CUDA(cudaMallocAsync(&Ls, sizeof(double) * 6 * (size_t)in.npts, st));
+        gsaft_launch_ip_part0(p, in, o, Ls, nullptr, st);
+        const bool vec = o.dpdT || o.d2PsirdTdrhoi || o.dpdrhovec || o.pmv || o.chempotVLE || o.dchempotdT || o.dlnphi_dT || o.dlnphi_drho || o.dlnphi_dv;
+        if (vec) gsaft_launch_ip_part1(p, in, o, Ls, nullptr, st);
+        if (o.dlnphi_dx) {
+            TQ_CUDA(cudaMallocAsync(&H, sizeof(double) * (size_t)nc * nc * (size_t)in.npts, st));
+            IsochoricOut io; io.hess = H;
+            gsaft_launch_isochoric(p, in, io, st);
+            gsaft_launch_ip_part2(p, in, o, Ls, H, st);
+            TQ_CUDA(cudaFreeAsync(H, st));
+        }
+        TQ_CUDA(cudaFreeAsync(Ls, st));
+    }
 };
 
 std::vector<std::vector<double>> square_matrix(const Json& j, size_t N, const char* what) {

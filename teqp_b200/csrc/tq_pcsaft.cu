@@ -14,6 +14,8 @@ void pcsaft_launch_ar_rho(const PcsaftParams&, int ND, const DeviceBatch&, doubl
 void pcsaft_launch_ar_mixed(const PcsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
 void pcsaft_launch_ATrhoXi(const PcsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void pcsaft_launch_isochoric(const PcsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void pcsaft_launch_cross2(const PcsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);   // tq_xx_pcsaft_{2,3}.cu (directional jets)
+void pcsaft_launch_cross3(const PcsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 void pcsaft_launch_sigma(const PcsaftParams&, const DeviceBatch&, const double*, double*, cudaStream_t);   // tq_ex_pcsaft.cu
 
 namespace {
@@ -63,6 +65,8 @@ public:
     }
     void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { launch_ar_table(NT, ND, in, out, st); }
     void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { pcsaft_launch_sigma(p, in, v, out, st); }
+    void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { pcsaft_launch_cross2(p, in, i, j, -1, out, st); }
+    void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { pcsaft_launch_cross3(p, in, i, j, k, out, st); }
     void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { pcsaft_launch_ATrhoXi(p, in, out, st); }
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override { pcsaft_launch_isoprops(p, in, o, st); }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { pcsaft_launch_isochoric(p, in, o, st); }

@@ -11,6 +11,7 @@
 #include "../../teqp_b200/csrc/tq_common.hpp"
 #include "../../teqp_b200/csrc/tq_cubic.cuh"
 #include "../../teqp_b200/csrc/tq_generic.cuh"
+#include "../../teqp_b200/csrc/tq_generic_dir.cuh"
 #include "../../teqp_b200/csrc/tq_gerg.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_iso.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_jet.cuh"
@@ -122,6 +123,16 @@ void gerg_ip_loop(const GergProgram& P, double Rgas, long long npts, const doubl
     for (long long k = 0; k < npts; ++k) {
         for (int i = 0; i < P.nc; ++i) W[(size_t)i * WS] = rv[(long long)i * npts + k];
         gerg_iso_point<WS, true>(P, K, Rgas, T[k], W.data(), none, k, npts, &ip);
+    }
+}
+// cross-composition tables by directional jets (tq_generic_dir.cuh): PC-SAFT, SAFT-VR-Mie
+template<class M>
+void dir_xx(const typename M::Params& p, int nc, int which, int i, int j, int k, long long npts, const double* T, const double* rho, const double* x, double* out) {
+    for (long long q = 0; q < npts; ++q) {
+        double xx[M::kMaxC];
+        for (int c = 0; c < nc; ++c) xx[c] = x[(long long)c * npts + q];
+        if (which == 2) dir_ATrhoXiXj_point<M, M::kMaxC>(p, nc, T[q], rho[q], xx, i, j, out + q, npts);
+        else dir_ATrhoXiXjXk_point<M, M::kMaxC>(p, nc, T[q], rho[q], xx, i, j, k, out + q, npts);
     }
 }
 // cross-composition tables: which = 2 -> (i, j) table [36][npts]; which = 3 -> (i, j, k) table [32][npts]
@@ -256,6 +267,8 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "PCSAFT") dir_xx<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") dir_xx<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -274,6 +287,19 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         o.chempotVLE = outs[6]; o.dchempotdT = outs[7]; o.dlnphi_dT = outs[8]; o.dlnphi_drho = outs[9]; o.dlnphi_dv = outs[10]; o.dlnphi_dx = outs[11];
         if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
+            // the three single-shape parts the product launches for this family (GsaftModel::launch_isoprops)
+            const GsaftParams& p = *static_cast<const GsaftParams*>(blob);
+            std::vector<double> Ls((size_t)6 * npts), H;
+            if (o.dlnphi_dx) { H.resize((size_t)ncomp * ncomp * npts); IsochoricOut io; io.hess = H.data(); generic_iso<GsaftDev>(p, ncomp, npts, T, rhovec, io); }
+            for (long long k = 0; k < npts; ++k) {
+                double r[GsaftDev::kMaxC];
+                for (int i = 0; i < ncomp; ++i) r[i] = rhovec[(long long)i * npts + k];
+                generic_ip_L_point<GsaftDev, GsaftDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), k, npts);
+                generic_ip_C_point<GsaftDev, GsaftDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), k, npts);
+                if (o.dlnphi_dx) generic_ip_X_point<GsaftDev, GsaftDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), H.data(), k, npts);
+            }
+        }
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
             // same dispatch as GergModel::launch_isoprops
