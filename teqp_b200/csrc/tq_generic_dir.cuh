@@ -30,59 +30,64 @@ TQ_HD J3<1, 1, NX> dir_jet(const typename M::Params& p, const int nc, const doub
     return embed<J3<1, 1, NX>>(M::template alphar<MAXN>(p, T, rho, x));
 }
 
+// The sweeps over the directions are a ROLLED loop (#pragma unroll 1) with the seeds chosen at run time, so the model code is instantiated
+// once per kernel -- inlining it 3 or 7 times is what NVVM did not finish compiling for these families.
+
 // out[((NT*2+ND)*3+NXi)*3+NXj][npts]
 template<class M, int MAXN>
 TQ_HD void dir_ATrhoXiXj_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin, const int i, const int j,
                                double* out, const long long ostride) {
-    const J3<1, 1, 2> ai = dir_jet<M, MAXN, 2>(p, nc, T0, rho0, xin, i, -1, -1);
-    const J3<1, 1, 2> aj = dir_jet<M, MAXN, 2>(p, nc, T0, rho0, xin, j, -1, -1);
-    const J3<1, 1, 2> aij = dir_jet<M, MAXN, 2>(p, nc, T0, rho0, xin, i, j, -1);
-    const double nan = ai.c[0].c[0].c[0] * 0.0 + (0.0 / 0.0);   // quiet NaN without a library call on either side
+    double c[3][4][3];   // [direction: e_i, e_j, e_i + e_j][(nt, nd)][order]
+#pragma unroll 1
+    for (int s = 0; s < 3; ++s) {
+        const J3<1, 1, 2> a = dir_jet<M, MAXN, 2>(p, nc, T0, rho0, xin, s == 1 ? j : i, s == 2 ? j : -1, -1);
 #pragma unroll
-    for (int nt = 0; nt <= 1; ++nt)
+        for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int nd = 0; nd <= 1; ++nd) {
-            double* o = out + (long long)((nt * 2 + nd) * 9) * ostride;
-            const double ci1 = ai.c[nt].c[nd].c[1], ci2 = ai.c[nt].c[nd].c[2], cj1 = aj.c[nt].c[nd].c[1], cj2 = aj.c[nt].c[nd].c[2];
-            o[0 * ostride] = ai.c[nt].c[nd].c[0];                         // (0,0)
-            o[1 * ostride] = cj1;                                         // (0,1)
-            o[2 * ostride] = 2.0 * cj2;                                   // (0,2)
-            o[3 * ostride] = ci1;                                         // (1,0)
-            o[4 * ostride] = aij.c[nt].c[nd].c[2] - ci2 - cj2;            // (1,1)
-            o[5 * ostride] = nan;                                         // (1,2)
-            o[6 * ostride] = 2.0 * ci2;                                   // (2,0)
-            o[7 * ostride] = nan;                                         // (2,1)
-            o[8 * ostride] = nan;                                         // (2,2)
-        }
+            for (int n = 0; n < 3; ++n) c[s][q][n] = a.c[q >> 1].c[q & 1].c[n];
+    }
+    const double nan = c[0][0][0] * 0.0 + (0.0 / 0.0);   // quiet NaN
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        double* o = out + (long long)(q * 9) * ostride;
+        o[0 * ostride] = c[0][q][0];                                   // (0,0)
+        o[1 * ostride] = c[1][q][1];                                   // (0,1)
+        o[2 * ostride] = 2.0 * c[1][q][2];                             // (0,2)
+        o[3 * ostride] = c[0][q][1];                                   // (1,0)
+        o[4 * ostride] = c[2][q][2] - c[0][q][2] - c[1][q][2];         // (1,1)
+        o[5 * ostride] = nan;                                          // (1,2)
+        o[6 * ostride] = 2.0 * c[0][q][2];                             // (2,0)
+        o[7 * ostride] = nan;                                          // (2,1)
+        o[8 * ostride] = nan;                                          // (2,2)
+    }
 }
 
 // out[(((NT*2+ND)*2+NXi)*2+NXj)*2+NXk][npts]
 template<class M, int MAXN>
 TQ_HD void dir_ATrhoXiXjXk_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin, const int i, const int j,
                                  const int kk, double* out, const long long ostride) {
-    const J3<1, 1, 3> ai = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, i, -1, -1);
-    const J3<1, 1, 3> aj = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, j, -1, -1);
-    const J3<1, 1, 3> ak = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, kk, -1, -1);
-    const J3<1, 1, 3> aij = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, i, j, -1);
-    const J3<1, 1, 3> aik = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, i, kk, -1);
-    const J3<1, 1, 3> ajk = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, j, kk, -1);
-    const J3<1, 1, 3> aijk = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, i, j, kk);
+    // directions, as bit masks over (i, j, k): 1 = e_i, 2 = e_j, 4 = e_k, 3 = e_i + e_j, 5, 6, 7
+    double c[8][4][4];   // [mask][(nt, nd)][order]
+#pragma unroll 1
+    for (int msk = 1; msk < 8; ++msk) {
+        const J3<1, 1, 3> a = dir_jet<M, MAXN, 3>(p, nc, T0, rho0, xin, (msk & 1) ? i : -1, (msk & 2) ? j : -1, (msk & 4) ? kk : -1);
 #pragma unroll
-    for (int nt = 0; nt <= 1; ++nt)
+        for (int q = 0; q < 4; ++q)
 #pragma unroll
-        for (int nd = 0; nd <= 1; ++nd) {
-            double* o = out + (long long)((nt * 2 + nd) * 8) * ostride;
-#define TQ_C(a, n) a.c[nt].c[nd].c[n]
-            o[0 * ostride] = TQ_C(ai, 0);                                                                  // 000
-            o[1 * ostride] = TQ_C(ak, 1);                                                                  // 001
-            o[2 * ostride] = TQ_C(aj, 1);                                                                  // 010
-            o[3 * ostride] = TQ_C(ajk, 2) - TQ_C(aj, 2) - TQ_C(ak, 2);                                     // 011
-            o[4 * ostride] = TQ_C(ai, 1);                                                                  // 100
-            o[5 * ostride] = TQ_C(aik, 2) - TQ_C(ai, 2) - TQ_C(ak, 2);                                     // 101
-            o[6 * ostride] = TQ_C(aij, 2) - TQ_C(ai, 2) - TQ_C(aj, 2);                                     // 110
-            o[7 * ostride] = TQ_C(aijk, 3) - TQ_C(aij, 3) - TQ_C(aik, 3) - TQ_C(ajk, 3) + TQ_C(ai, 3) + TQ_C(aj, 3) + TQ_C(ak, 3);   // 111
-#undef TQ_C
-        }
+            for (int n = 0; n < 4; ++n) c[msk][q][n] = a.c[q >> 1].c[q & 1].c[n];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        double* o = out + (long long)(q * 8) * ostride;
+        o[0 * ostride] = c[1][q][0];                                                                                         // 000
+        o[1 * ostride] = c[4][q][1];                                                                                         // 001
+        o[2 * ostride] = c[2][q][1];                                                                                         // 010
+        o[3 * ostride] = c[6][q][2] - c[2][q][2] - c[4][q][2];                                                               // 011
+        o[4 * ostride] = c[1][q][1];                                                                                         // 100
+        o[5 * ostride] = c[5][q][2] - c[1][q][2] - c[4][q][2];                                                               // 101
+        o[6 * ostride] = c[3][q][2] - c[1][q][2] - c[2][q][2];                                                               // 110
+        o[7 * ostride] = c[7][q][3] - c[3][q][3] - c[5][q][3] - c[6][q][3] + c[1][q][3] + c[2][q][3] + c[4][q][3];           // 111
+    }
 }
 
 #if defined(__CUDACC__)

@@ -23,12 +23,12 @@ def test_isochoric(emul, oracle, name):
     ps.isochoric(ps.EmulBackend(emul), oracle, name, n=300)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_cross_composition(emul, oracle, name):
     ps.cross_composition(ps.EmulBackend(emul), oracle, name, n=100)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isoprops(emul, oracle, name):
     ps.isoprops(ps.EmulBackend(emul), oracle, name, n=(30 if name == "GERG21" else 100))
 

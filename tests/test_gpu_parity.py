@@ -38,12 +38,12 @@ def test_isochoric(be, oracle, name):
     ps.isochoric(be, oracle, name, n=600)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "GERG2004_3", "GERG_H2O_CO2", "PCSAFT2", "PCSAFT3k", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_cross_composition(be, oracle, name):
     ps.cross_composition(be, oracle, name, n=200)
 
 
-@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21"])
+@pytest.mark.parametrize("name", ["PR2k", "SRK3", "PCSAFT2", "PCSAFT3k", "GERG2004_3", "GERG_H2O_CO2", "GERG10", "GERG21", "MIE3", "GSAFT_C4", "GSAFT_CR1"])
 def test_isoprops(be, oracle, name):
     ps.isoprops(be, oracle, name, n=(60 if name == "GERG21" else 300))
 
