@@ -347,12 +347,14 @@ def run_ours(args):
         I = synth(w, P, a)
         alloc, step, rows_out = make_steps(w, model, nc, P, "torch")
         O = alloc(lambda shape: torch.empty(shape, dtype=torch.float64, device=dev))
-        for _ in range(warmup):
-            step(I, O)
-        barrier()
+        # clocks / throttle reasons are sampled from the warm-up steps on (same kernel, same load): the timed region of the headline is ~0.1 s,
+        # one nvidia-smi sample at its 100 ms period
         sampler = ClockSampler(local) if sample_clocks else None
         if sampler:
             sampler.start()
+        for _ in range(warmup):
+            step(I, O)
+        barrier()
         l0 = teqp_b200.kernel_launches()
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
         ev[0].record()

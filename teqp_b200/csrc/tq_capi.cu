@@ -536,19 +536,19 @@ int get_Arxy_batch(const long long int uuid, const int npairs, const int* NT, co
             else if (nt <= 2 && nd <= 4) { where[p] = 2; blkNT = std::max(blkNT, nt); blkND = std::max(blkND, nd); }
             else throw InvalidArgument("mixed derivative (" + std::to_string(nt) + "," + std::to_string(nd) + ") is outside the compiled sweeps: NT = 0 with ND <= 6, ND = 0 with NT <= 4, or NT <= 2 with ND <= 4");
         }
-        // a pair of the row / column that the block sweep covers anyway rides along with it
+        // when a mixed block is needed anyway it grows to absorb the row / column pairs it can hold (one (2,2) sweep is cheaper than a (1,1),
+        // a (0,2) and a (2,0) sweep); what remains outside (ND > 4 on the row, NT > 2 on the column) keeps its own sweep
         if (blkNT >= 0) {
-            bool row_needed = false, col_needed = false;
+            rowND = -1; colNT = -1;
             for (int p = 0; p < npairs; ++p) {
-                if (where[p] == 0 && ND[p] > blkND) row_needed = true;
-                if (where[p] == 1 && NT[p] > blkNT) col_needed = true;
+                if (where[p] == 0 && ND[p] <= 4) { where[p] = 2; blkND = std::max(blkND, ND[p]); }
+                else if (where[p] == 1 && NT[p] <= 2) { where[p] = 2; blkNT = std::max(blkNT, NT[p]); }
             }
             for (int p = 0; p < npairs; ++p) {
-                if (where[p] == 0 && !row_needed) where[p] = 2;
-                if (where[p] == 1 && !col_needed) where[p] = 2;
+                if (where[p] == 0) rowND = std::max(rowND, ND[p]);
+                if (where[p] == 1) colNT = std::max(colNT, NT[p]);
             }
-            if (!row_needed) rowND = -1;
-            if (!col_needed) colNT = -1;
+            // a leftover row / column sweep also serves the lower orders of its own axis: no change needed, they were moved to the block
         }
         const bool bc = flags & TEQPB200_BROADCAST_X;
         const int rows_row = rowND >= 0 ? rowND + 1 : 0, rows_col = colNT >= 0 ? colNT + 1 : 0, rows_blk = blkNT >= 0 ? (blkNT + 1) * (blkND + 1) : 0;

@@ -235,7 +235,7 @@ def cross_composition(be, oracle, name, n=200):
                 S = np.maximum(np.max([np.abs(refs[d]) for d in COMBOS_XIXJXK if d[0] <= c[0] and d[1] <= c[1]], axis=0), extra_scale(name))
                 # PC-SAFT / SAFT families form the mixed partials by polarisation of directional jets (tq_generic_dir.cuh): the differences cancel
                 # to eps x the largest PURE directional third derivative, which the reference's table of mixed entries (the scale S) does not contain
-                pol = 4.0 if name.startswith(("PCSAFT", "MIE", "GSAFT")) else 1.0
+                pol = 8.0 if name.startswith(("PCSAFT", "MIE", "GSAFT")) else 1.0
                 parity.check("%s ATrhoXiXjXk NT%d ND%d %d%d%d" % (name, c[0], c[1], c[2], c[3], c[4]), got[c[0], c[1], c[2], c[3], c[4]], refs[c], S, ftol=4 * pol * ftol_for(name, c[1]),
                              max_floor_frac=floor_limit(name, sum(c)))
 

@@ -294,7 +294,7 @@ def test_arxy_batch_mixed_axis_pair_lists(be, oracle, name):
             want = t06[nd] if nt == 0 and nd > 4 else t40[nt] if nd == 0 and nt > 2 else blk[nt, nd]
             ref = t06[nd] if nt == 0 else t40[nt] if nd == 0 else blk[nt, nd]
             # different sweeps may serve the same entry: equal to the parity rule's floor, not bit for bit
-            fam = np.maximum(np.abs(ref), parity.coeff_scale(t06[None]) * parity.fact(nt, nd))
+            fam = np.maximum(np.abs(ref), np.maximum(parity.coeff_scale(t06[None]), ps.extra_scale(name)) * parity.fact(nt, nd))
             parity.check("%s Arxy_batch (%d,%d)" % (name, nt, nd), got[q], ref, fam, ftol=max(ps.ftol_for(name, nd), 1e-13))
     for bad in ([(3, 1)], [(1, 5)], [(0, 7)], [(5, 0)]):
         with pytest.raises(teqp_b200.TeqpError):
