@@ -8,7 +8,7 @@ mkdir -p $O
 nvidia-smi topo -m > $O/topo.txt 2>&1
 timeout 600 python -m pytest tests -m gpu -q -k "sharder or error_path" > $O/pytest_sharder.log 2>&1; echo "pytest sharder rc=$?"; tail -3 $O/pytest_sharder.log
 timeout 300 python tools/pcie_probe.py --gpus $N > $O/pcie_probe.jsonl 2> $O/pcie_probe.err; cat $O/pcie_probe.jsonl
-NS="1 $N"; if [ $N -eq 8 ]; then NS="1 2 4 8"; fi; if [ $N -eq 4 ]; then NS="1 2 4"; fi
+NS="1 $N"; if [ $N -eq 8 ]; then NS="4 8"; fi; if [ $N -eq 4 ]; then NS="1 2 4"; fi
 for n in $NS; do
   if [ $n -eq 1 ]; then L="python"; else L="python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517"; fi
   timeout 900 $L bench.py --gpus $n --steps 5 --warmup 3 --no-secondary > $O/bench_n$n.json 2> $O/bench_n$n.err; echo "bench n=$n rc=$?"
