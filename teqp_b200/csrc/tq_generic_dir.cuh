@@ -112,4 +112,74 @@ void dir_launch_cross(const typename M::Params& p, int nc, const DeviceBatch& in
 }
 #endif
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// get_ATrhoXi table by three SMALL jets instead of one rectangular J3<2,2,3> (36 coefficients per number: 40 KB of local memory per thread and
+// 15 instruction-fetch stall cycles per issue for SAFT-VR-Mie + association, profiles/r01j).  The reference's 23 combinations need
+// NT + ND <= 2, i.e. the (1/T, rho) blocks {(2,0)}, {(0,2)}, {(0,0),(1,0),(0,1),(1,1)} -- each with NXi <= 3:
+//     part 0: J3<1,1,3> (16 coefficients) -> entries nt <= 1, nd <= 1      part 1: J3<2,0,3> (12) -> nt = 2, nd = 0      part 2: J3<0,2,3> (12) -> nt = 0, nd = 2
+// Multiplication cost 90 + 60 + 60 against 360 for the rectangular jet, and every number fits the register file.  The entries of the table
+// with NT + ND > 2, which no reference entry point exposes, are NaN (part 0 writes them).
+// out[((i*3+nt)*3+nd)*4+nxi][npts]
+// ------------------------------------------------------------------------------------------------------------------
+template<class M, int MAXN, int CT, int CD>
+TQ_HD void split_ATrhoXi_point(const typename M::Params& p, const int nc, const double T0, const double rho0, const double* xin, double* out,
+                               const long long ostride) {
+    using XT = J3<0, 0, 3>;
+    using TT = J3<CT, 0, 0>;
+    using RT = J3<0, CD, 0>;
+    const TT T = TT::reciprocal_scaled_variable(T0);
+    RT rho;
+    rho.c[0] = Tay<CD, Tay<0, double>>::scaled_variable(rho0);
+#pragma unroll 1
+    for (int i = 0; i < nc; ++i) {
+        XT x[MAXN];
+        for (int j = 0; j < nc; ++j) {
+            x[j] = XT(xin[j]);
+            if (j == i) x[j].c[0].c[0].c[1] = 1.0;
+        }
+        const J3<CT, CD, 3> a = embed<J3<CT, CD, 3>>(M::template alphar<MAXN>(p, T, rho, x));
+        double* o = out + (long long)(i * 36) * ostride;
+#pragma unroll
+        for (int nx = 0; nx <= 3; ++nx) {
+            const double fx = (nx == 2 ? 2.0 : (nx == 3 ? 6.0 : 1.0));
+            if constexpr (CT == 1 && CD == 1) {
+                const double nan = a.c[0].c[0].c[0] * 0.0 + (0.0 / 0.0);
+#pragma unroll
+                for (int nt = 0; nt <= 2; ++nt)
+#pragma unroll
+                    for (int nd = 0; nd <= 2; ++nd) {
+                        if (nt <= 1 && nd <= 1) o[(long long)((nt * 3 + nd) * 4 + nx) * ostride] = fx * a.c[nt].c[nd].c[nx];
+                        else if (nt + nd > 2) o[(long long)((nt * 3 + nd) * 4 + nx) * ostride] = nan;
+                    }
+            } else if constexpr (CT == 2) {
+                o[(long long)((2 * 3 + 0) * 4 + nx) * ostride] = 2.0 * fx * a.c[2].c[0].c[nx];
+            } else {
+                o[(long long)((0 * 3 + 2) * 4 + nx) * ostride] = 2.0 * fx * a.c[0].c[2].c[nx];
+            }
+        }
+    }
+}
+
+#if defined(__CUDACC__)
+template<class M, int CT, int CD>
+__global__ void __launch_bounds__(64) split_ATrhoXi_kernel(const __grid_constant__ typename M::Params p, const int nc, const DeviceBatch in,
+                                                           double* __restrict__ out) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        double x[M::kMaxC];
+        load_x<M, M::kMaxC>(x, nc, in, k);
+        split_ATrhoXi_point<M, M::kMaxC, CT, CD>(p, nc, __ldg(in.T + k), __ldg(in.rho + k), x, out + k, npts);
+    }
+}
+template<class M, int CT, int CD>
+void split_launch_ATrhoXi(const typename M::Params& p, int nc, const DeviceBatch& in, double* out, cudaStream_t st) {
+    if (in.npts == 0) return;
+    const int block = 64;
+    split_ATrhoXi_kernel<M, CT, CD><<<grid_for(in.npts, block, sm_count() * 32), block, 0, st>>>(p, nc, in, out);
+    TQ_CUDA(cudaGetLastError());
+}
+#endif
+
 }  // namespace tq

@@ -9,6 +9,8 @@
 #include <set>
 
 #include "tq_assoc.cuh"
+#include <cstdlib>
+
 #include "tq_common.hpp"
 #include "tq_generic.cuh"
 #include "tq_mie.cuh"
@@ -20,6 +22,9 @@ void gsaft_launch_ar_rho(const GsaftParams&, int ND, const DeviceBatch&, double*
 void gsaft_launch_ar_mixed(const GsaftParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_ATrhoXi(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_isochoric(const GsaftParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void gsaft_launch_ATrhoXi_part0(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);   // tq_ax_gsaft_{0,1,2}.cu
+void gsaft_launch_ATrhoXi_part1(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);
+void gsaft_launch_ATrhoXi_part2(const GsaftParams&, const DeviceBatch&, double*, cudaStream_t);
 void gsaft_launch_cross2(const GsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);   // tq_xx_gsaft_{2,3}.cu (directional jets)
 void gsaft_launch_cross3(const GsaftParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
 void gsaft_launch_sigma(const GsaftParams&, const DeviceBatch&, const double*, double*, cudaStream_t);   // tq_ex_gsaft.cu
@@ -63,7 +68,14 @@ public:
     void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { gsaft_launch_sigma(p, in, v, out, st); }
     void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { gsaft_launch_cross2(p, in, i, j, -1, out, st); }
     void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { gsaft_launch_cross3(p, in, i, j, k, out, st); }
-    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override { gsaft_launch_ATrhoXi(p, in, out, st); }
+    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override {
+        // three small-jet kernels (tq_generic_dir.cuh); TEQPB200_ATRHOXI_RECT runs the rectangular J3<2,2,3> sweep of round 1 (A/B)
+        static const bool rect = std::getenv("TEQPB200_ATRHOXI_RECT") != nullptr;
+        if (rect) { gsaft_launch_ATrhoXi(p, in, out, st); return; }
+        gsaft_launch_ATrhoXi_part0(p, in, out, st);
+        gsaft_launch_ATrhoXi_part1(p, in, out, st);
+        gsaft_launch_ATrhoXi_part2(p, in, out, st);
+    }
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { gsaft_launch_isochoric(p, in, o, st); }
     // derived isochoric properties: three single-shape kernels + the Hessian of the isochoric kernel (scratch on the stream)
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {

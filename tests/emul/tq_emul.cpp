@@ -251,7 +251,17 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
-        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_atrhoxi<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
+            // the three small-jet parts the product launches for this family (GsaftModel::launch_ATrhoXi_table)
+            const GsaftParams& p = *static_cast<const GsaftParams*>(blob);
+            for (long long k = 0; k < npts; ++k) {
+                double xx[GsaftDev::kMaxC];
+                for (int i = 0; i < ncomp; ++i) xx[i] = x[(long long)i * npts + k];
+                split_ATrhoXi_point<GsaftDev, GsaftDev::kMaxC, 1, 1>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+                split_ATrhoXi_point<GsaftDev, GsaftDev::kMaxC, 2, 0>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+                split_ATrhoXi_point<GsaftDev, GsaftDev::kMaxC, 0, 2>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+            }
+        }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
