@@ -117,7 +117,7 @@ public:
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {
         // analytic pass (tq_gerg_iso.cuh) where it applies; TEQPB200_GERG_ISOPROPS_JETS forces the jet sweeps (A/B and cross-check)
         static const bool jets = std::getenv("TEQPB200_GERG_ISOPROPS_JETS") != nullptr;
-        if (!jets && src.all_plain_tau && !P.r_weighted && !P.pure_shortcut) gerg_launch_isoprops(P, Rgas, in, o, st);
+        if (!jets && src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) gerg_launch_isoprops(P, Rgas, in, o, st);
         else gergjet_launch_isoprops(P, in, o, st);
     }
     // GERG200XReducing::get_Tr / get_rhor (GERG.hpp:179-205) on the host, same pair order and skip rule as the kernels
@@ -143,7 +143,7 @@ public:
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         // the analytic kernel (tq_gerg_iso.cuh) knows tau^t temperature shapes and a constant R; JSON multifluid models with Gaussian /
         // GaoB / Lemmon2005 terms or the mole-fraction-weighted R go through the jet sweeps
-        if (src.all_plain_tau && !P.r_weighted && !P.pure_shortcut) gerg_launch_isochoric(P, Rgas, in, o, st);
+        if (src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) gerg_launch_isochoric(P, Rgas, in, o, st);
         else gergjet_launch_isochoric(P, in, o, st);
     }
     void launch_Ataudelta_table(int which, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override {
@@ -191,7 +191,7 @@ public:
         if (in.npts == 0) return;
         if (NT < 0 || ND < 0 || !shape_ok(NT, ND))
             throw InvalidArgument("derivative table (" + std::to_string(NT) + "," + std::to_string(ND) + ") is not a supported shape for " + fam);
-        if (NT > 0 && !src.all_plain_tau) {
+        if ((NT > 0 && !src.all_plain_tau) || src.has_nonanalytic) {
             // temperature derivatives of Gaussian / GaoB / Lemmon2005 temperature shapes are not binomial factors: jet sweep
             gergjet_launch_virial(P, NT, ND, in, out, st);
             return;
@@ -292,6 +292,9 @@ std::unique_ptr<Model> make_term_program_model(const TermProgramInput& in) {
     P.pure_shortcut = (in.pure_shortcut && N == 1) ? 1 : 0;
     m->Ri = in.Ri;
     for (size_t i = 0; i < N; ++i) { P.Tc[i] = in.Tc[i]; P.vc[i] = in.vc[i]; if (in.r_weighted) P.Ri[i] = in.Ri.at(i); }
+    if (in.na.size() > (size_t)kGergMaxNA) throw InvalidArgument("too many non-analytic terms for the device term program");
+    P.nna = (int)in.na.size();
+    for (size_t q = 0; q < in.na.size(); ++q) P.na[q] = in.na[q];
 
     std::vector<RawTerm> raw = in.pure;
     int pidx = 0, ndep = 0;
@@ -322,6 +325,7 @@ std::unique_ptr<Model> make_term_program_model(const TermProgramInput& in) {
         for (int q = 0; q < ndep; ++q) { S.dep_i.push_back(P.dep_i[q]); S.dep_j.push_back(P.dep_j[q]); S.depF.push_back(P.depF[q]); }
         S.terms = raw;
         for (const auto& r : raw) if (r.tk != GT_PLAIN) S.all_plain_tau = false;
+        S.has_nonanalytic = P.nna > 0;
     }
 
     // non-plain temperature shapes

@@ -47,6 +47,11 @@ enum GergGroupKind : int { GG_POLY = 0, GG_EXP = 1, GG_GAUSS = 2 };
 enum GergTauKind : int { GT_PLAIN = 0, GT_GAUSS = 1, GT_GAOB = 2, GT_POWEXP = 3 };
 struct GergTauFn { int kind, pad_; double p1, p2, p3; };
 constexpr int kGergMaxTF = 40;   // distinct non-plain temperature shapes per model
+// Non-analytic critical-region terms (NonAnalyticEOSTerm, multifluid_eosterms.hpp:335-362; CO2, water):
+//   n delta Delta^b exp(-C (delta-1)^2 - D (tau-1)^2),  Delta = theta^2 + B ((delta-1)^2)^a,  theta = (1 - tau) + A ((delta-1)^2)^(1/(2 beta))
+// tau and delta do not separate, so these are evaluated by the jet sweeps only (a model that has them runs no generated / analytic kernel)
+struct GergNA { double n, A, B, C, D, a, b, beta; int w, pad_; };
+constexpr int kGergMaxNA = 8;
 
 struct GergGroup {
     int kind;        // GG_POLY: delta^d ; GG_EXP: delta^d exp(-c delta^l) ; GG_GAUSS: delta^d exp(-eta(delta-eps)^2 - beta(delta-gamma))
@@ -87,8 +92,10 @@ struct GergProgram {
     int pure_shortcut;  // 1: single component: the mole fraction does not multiply the pure-fluid sum (multifluid.hpp:172-175)
     double Ri[kGergMaxC];
     GergTauFn tf[kGergMaxTF];
+    int nna, pad2_;     // non-analytic terms in na[]
+    GergNA na[kGergMaxNA];
 };
-static_assert(sizeof(GergProgram) <= 32600, "GergProgram must fit in the 32 KB kernel-parameter space (32764 B)");
+static_assert(sizeof(GergProgram) <= 32500, "GergProgram must fit in the 32 KB kernel-parameter space (32764 B)");
 
 TQ_HD double wload(const double* W, int byte_offset) {
     return *reinterpret_cast<const double*>(reinterpret_cast<const char*>(W) + byte_offset);

@@ -65,6 +65,20 @@ TQ_HD prom_t<TX, RX> gerg_alphar_taudelta_jet(const GergProgram& P, const TX& ta
         }
         A = A + C * G;
     }
+    // non-analytic terms (multifluid_eosterms.hpp:335-362); a non-finite value (the critical point itself) counts as zero, as in the reference
+    for (int q = 0; q < P.nna; ++q) {
+        const GergNA t = P.na[q];
+        const RX dm1 = delta - 1.0;
+        const RX d2 = dm1 * dm1;
+        const TX tm1 = tau - 1.0;
+        const F Psi = texp(embed<F>(d2 * (-t.C)) - embed<F>((tm1 * tm1) * t.D));
+        const F theta = embed<F>(1.0 - tau) + embed<F>(tpow(d2, 1.0 / (2.0 * t.beta)) * t.A);
+        const F Delta = theta * theta + embed<F>(tpow(d2, t.a) * t.B);
+        F term = (tpow(Delta, t.b) * Psi) * delta;
+        const double bv = base(term);
+        if (!(bv - bv == 0.0)) term = F(0.0);
+        A = A + term * (W[t.w] * t.n);
+    }
     return A;
 }
 

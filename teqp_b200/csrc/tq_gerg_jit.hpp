@@ -37,6 +37,7 @@ struct GergSource {
     int nc = 0, ndep = 0;
     bool pure_shortcut = false;   // single-component multifluid: the mole fraction does not multiply the sum (multifluid.hpp:172-175)
     bool all_plain_tau = true;    // no term has a non-plain temperature shape (then temperature derivatives are binomial factors)
+    bool has_nonanalytic = false; // the model has non-analytic terms: jet sweeps only
     std::vector<double> Tc, vc;
     std::vector<GergRedPair> pair;
     std::vector<int> dep_i, dep_j;
@@ -68,6 +69,7 @@ struct TermProgramInput {
     };
     std::vector<Pair> pairs;
     std::vector<GergTerm> pure;          // w = component index
+    std::vector<GergNA> na;              // non-analytic terms (w = component index)
     double Rgas = 0;                     // constant gas constant ...
     std::vector<double> Ri;              // ... or per-fluid values, mole-fraction weighted when r_weighted
     bool r_weighted = false, limit_form = false, pure_shortcut = false;

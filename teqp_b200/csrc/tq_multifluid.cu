@@ -83,7 +83,7 @@ GergTerm power_term(double n, double t, double d, double c, double l) {
 }
 
 // The terms of one "alphar" array of a fluid file (get_EOS_terms, multifluid.hpp:530-819)
-void add_pure_terms(const Json& alphar, int w, std::vector<GergTerm>& out) {
+void add_pure_terms(const Json& alphar, int w, std::vector<GergTerm>& out, std::vector<GergNA>& na) {
     if (!alphar.is_array() || alphar.size() == 0) throw InvalidArgument("alphar array cannot be empty");
     for (size_t q = 0; q < alphar.size(); ++q) {
         const Json& term = alphar[q];
@@ -146,8 +146,13 @@ void add_pure_terms(const Json& alphar, int w, std::vector<GergTerm>& out) {
                 if (gt[k] != 0.0) { r.tk = GT_POWEXP; r.tp1 = gt[k]; r.tp2 = lt[k]; }
                 out.push_back(r);
             }
-        } else if (type == "ResidualHelmholtzNonAnalytic" || type == "ResidualHelmholtzGenericCubic" || type == "ResidualHelmholtzPCSAFTGrossSadowski2001") {
-            throw NotImplementedError("multifluid term type " + type + " does not factorise into density x temperature shapes and is not implemented in libteqpb200");
+        } else if (type == "ResidualHelmholtzNonAnalytic") {
+            same_length(term, {"n", "A", "B", "C", "D", "a", "b", "beta"}, "nonanalytic");
+            const auto n = term.at("n").as_doubles(), A = term.at("A").as_doubles(), B = term.at("B").as_doubles(), Cc = term.at("C").as_doubles(),
+                       D = term.at("D").as_doubles(), a = term.at("a").as_doubles(), b = term.at("b").as_doubles(), beta = term.at("beta").as_doubles();
+            for (size_t k = 0; k < n.size(); ++k) na.push_back(GergNA{n[k], A[k], B[k], Cc[k], D[k], a[k], b[k], beta[k], w, 0});
+        } else if (type == "ResidualHelmholtzGenericCubic" || type == "ResidualHelmholtzPCSAFTGrossSadowski2001") {
+            throw NotImplementedError("multifluid pseudo-term type " + type + " is not implemented in libteqpb200");
         } else {
             throw InvalidArgument("Bad term type: " + type);
         }
@@ -284,7 +289,7 @@ std::unique_ptr<Model> make_multifluid_model(const Json& spec) {
         in.Tc.push_back(red.at("T").as_double());
         in.vc.push_back(1.0 / red.at("rhomolar").as_double());
         in.Ri.push_back(eos.at("gas_constant").as_double());
-        add_pure_terms(eos.at("alphar"), (int)i, in.pure);
+        add_pure_terms(eos.at("alphar"), (int)i, in.pure, in.na);
         const Json& info = pure[i].at("INFO");
         idName.push_back(info.at("NAME").as_string());
         idCAS.push_back(info.at("CAS").as_string());

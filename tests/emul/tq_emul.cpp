@@ -313,7 +313,7 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
             // same dispatch as GergModel::launch_isoprops
-            if (P.ntf == 0 && !P.r_weighted && !P.pure_shortcut && !std::getenv("TEQPB200_GERG_ISOPROPS_JETS")) gerg_ip_loop(P, P.Rgas, npts, T, rhovec, o);
+            if (P.ntf == 0 && P.nna == 0 && !P.r_weighted && !P.pure_shortcut && !std::getenv("TEQPB200_GERG_ISOPROPS_JETS")) gerg_ip_loop(P, P.Rgas, npts, T, rhovec, o);
             else generic_ip<GergJetDev>(P, ncomp, npts, T, rhovec, o);
         }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
@@ -336,7 +336,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
             // same dispatch as GergModel::launch_isochoric: analytic kernel for tau^t shapes and a constant R, jet sweeps otherwise
-            if (P.ntf == 0 && !P.r_weighted && !P.pure_shortcut) gerg_iso_loop(P, P.Rgas, npts, T, rhovec, o);
+            if (P.ntf == 0 && P.nna == 0 && !P.r_weighted && !P.pure_shortcut) gerg_iso_loop(P, P.Rgas, npts, T, rhovec, o);
             else generic_iso<GergJetDev>(P, ncomp, npts, T, rhovec, o);
         }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);

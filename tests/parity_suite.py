@@ -119,6 +119,7 @@ class GpuBackend:
 # families get ATOL = 2 x (sum of the two columns) as an additional absolute floor (in coefficient space, i.e. times n! m!).
 ATOL_FAMILY = {"MIE1": 1.3e-13, "MIE3": 1.3e-13, "GSAFT_CR1": 3e-13, "GSAFT_C4": 5e-12, "GSAFT_WATER": 8e-11}
 ADJ_FACTOR = {"MIE1": 3.0, "MIE3": 3.0, "GSAFT_C4": 3.0, "GSAFT_CR1": 3.0, "GSAFT_WATER": 3.0,
+              "MF_CO2_N2": 3.0,      # non-analytic terms: pow chains on jets; 3.2e-14 S against the reference's 1.5e-14 S on Ar24
               "MF_R32_R125": 10.0}   # orders 5 and 6 of get_Ar06n only (density exponents up to 8 through binomials): 1.3e-14 S against the reference's 1.6e-15 S
 
 

@@ -61,7 +61,7 @@ def test_sigma_derivs(emul, oracle, name):
     ps.sigma_derivs(ps.EmulBackend(emul), oracle, name, n=200)
 
 
-MF_CASES = ["MF_CH4_N2_O2", "MF_CH4_C2H6_CODATA", "MF_N2", "MF_R32_R125", "MF_NH3_AR"]
+MF_CASES = ["MF_CH4_N2_O2", "MF_CH4_C2H6_CODATA", "MF_N2", "MF_R32_R125", "MF_NH3_AR", "MF_CO2_N2"]
 
 
 @pytest.mark.parametrize("name", MF_CASES)

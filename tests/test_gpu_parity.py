@@ -239,7 +239,7 @@ def test_cpp_abstractmodel_adapter():
     assert r.returncode == 0, r.stdout[-3000:]
 
 
-MF_CASES = ["MF_CH4_N2_O2", "MF_CH4_C2H6_CODATA", "MF_N2", "MF_R32_R125", "MF_NH3_AR"]
+MF_CASES = ["MF_CH4_N2_O2", "MF_CH4_C2H6_CODATA", "MF_N2", "MF_R32_R125", "MF_NH3_AR", "MF_CO2_N2"]
 
 
 @pytest.mark.parametrize("name", MF_CASES)

@@ -47,6 +47,8 @@ out = {
     "MF_N2": spec(["Nitrogen"]),
     # Lemmon2005 (R125) + Exponential-type departure (R32-R125)
     "MF_R32_R125": spec(["R32", "R125"]),
+    # non-analytic critical-region terms (CO2 of Span-Wagner) with nitrogen and a GERG-2008 departure function: jet sweeps only
+    "MF_CO2_N2": spec(["CarbonDioxide", "Nitrogen"]),
     # GaoB terms (ammonia 2020) with argon; Lorentz-Berthelot estimate for the missing pair
     "MF_NH3_AR": spec(["Ammonia", "Argon"], {"estimate": "Lorentz-Berthelot"}),
 }
