@@ -87,6 +87,8 @@ public:
     // Lambda^r_{nm} for every 0<=n<=NT, 0<=m<=ND in one sweep: out[(n*(ND+1)+m)][npts]
     // (reference: derivs.hpp:150-238 get_Agenxy, :543-624 get_Ar0n / get_Arn0)
     virtual void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const = 0;
+    // false: launch_ar_table(NT, ND, ...) would first have to generate / load a kernel (which allocates); asked by the no-allocation entry point
+    virtual bool ar_table_ready(int NT, int ND) const { (void)NT; (void)ND; return true; }
 
     // composition-derivative table (derivs.hpp:247-292): for each component i and each (NT,ND,NXi) with NT+ND<=2, NXi<=3:
     // out[((i*3+nt)*3+nd)*4+nxi][npts] = (1/T)^nt rho^nd d^(nt+nd+nxi) alphar / d(1/T)^nt drho^nd dx_i^nxi

@@ -13,6 +13,7 @@
 #include "tq_common.hpp"
 #include "tq_gerg.cuh"
 #include "tq_gerg_iso.cuh"
+#include "tq_gerg_iso_coop.cuh"
 #include "tq_gerg_jit.hpp"
 
 namespace tq {
@@ -100,6 +101,12 @@ public:
     std::vector<double> Ri;  // per-fluid gas constants (multifluid, mole-fraction weighted)
     std::string fam, meta_json = "{}";
     std::string meta() const override { return meta_json; }
+    GergIsoDeviceTables iso_tab;   // tables of the lane-cooperative isochoric kernels (tq_gerg_iso_coop.cuh), built and uploaded at first use
+    // TEQPB200_ISO_COOP_MINROWS: use the lane-cooperative form only for mixtures whose thread-per-point staging area has at least this many rows
+    bool coop_pays() const {
+        static const int min_rows = [] { const char* e = std::getenv("TEQPB200_ISO_COOP_MINROWS"); return e ? std::atoi(e) : 0; }();
+        return gerg_iso_rows(P.nc, P.nw, true) >= min_rows;
+    }
     bool taudelta_ok() const { return fam == "multifluid"; }   // the reference's GERG2008ResidualModel has no alphar_taudelta (derivs.hpp:137-140)
     int ncomp() const override { return P.nc; }
     const char* family() const override { return fam.c_str(); }
@@ -117,7 +124,9 @@ public:
     void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {
         // analytic pass (tq_gerg_iso.cuh) where it applies; TEQPB200_GERG_ISOPROPS_JETS forces the jet sweeps (A/B and cross-check)
         static const bool jets = std::getenv("TEQPB200_GERG_ISOPROPS_JETS") != nullptr;
-        if (!jets && src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) gerg_launch_isoprops(P, Rgas, in, o, st);
+        if (!jets && src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) {
+            if (!coop_pays() || !gerg_coop_launch_isoprops(iso_tab, P, Rgas, in, o, st)) gerg_launch_isoprops(P, Rgas, in, o, st);
+        }
         else gergjet_launch_isoprops(P, in, o, st);
     }
     // GERG200XReducing::get_Tr / get_rhor (GERG.hpp:179-205) on the host, same pair order and skip rule as the kernels
@@ -143,7 +152,9 @@ public:
     void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override {
         // the analytic kernel (tq_gerg_iso.cuh) knows tau^t temperature shapes and a constant R; JSON multifluid models with Gaussian /
         // GaoB / Lemmon2005 terms or the mole-fraction-weighted R go through the jet sweeps
-        if (src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) gerg_launch_isochoric(P, Rgas, in, o, st);
+        if (src.all_plain_tau && !src.has_nonanalytic && !P.r_weighted && !P.pure_shortcut) {
+            if (!coop_pays() || !gerg_coop_launch_isochoric(iso_tab, P, Rgas, in, o, st)) gerg_launch_isochoric(P, Rgas, in, o, st);
+        }
         else gergjet_launch_isochoric(P, in, o, st);
     }
     void launch_Ataudelta_table(int which, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override {
@@ -176,6 +187,12 @@ public:
             j.k = jit_compile(j.s.code, "tqj_kernel", nullptr, nullptr, true);
         }
         return j;
+    }
+    bool ar_table_ready(int NT, int ND) const override {
+        if ((NT > 0 && !src.all_plain_tau) || src.has_nonanalytic) return true;   // jet sweep: a compiled-in kernel
+        std::lock_guard<std::mutex> g(jit_mtx);
+        auto it = jit.find({NT, ND});
+        return it != jit.end() && it->second.k != nullptr;
     }
     std::string jit_source(int NT, int ND, std::vector<double>* consts) const override {
         JitSource s = gerg_generate(src, NT, ND);

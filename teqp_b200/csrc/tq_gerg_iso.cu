@@ -1,6 +1,9 @@
 // GERG-2004/2008 isochoric family on the device: one state point per thread, per-thread working set in a column of the CTA's
 // shared staging area (see tq_gerg_iso.cuh for the mathematics and the reference lines it replaces).
 #include "tq_gerg_iso.cuh"
+#include "tq_gerg_iso_coop.cuh"
+
+#include <cstdlib>
 
 namespace tq {
 
@@ -72,6 +75,100 @@ void launch_ip(const GergProgram& P, double Rgas, const DeviceBatch& in, const I
 }
 
 }  // namespace
+
+// ---- lane-cooperative kernels (tq_gerg_iso_coop.cuh) ----------------------------------------------------------------------------
+namespace {
+
+constexpr int kCoopMaxWarps = 16;   // 512 threads: 128 registers per thread
+
+// persistent CTA: the per-model tables go to shared memory once, then every warp walks its share of the batch, 32 / L points at a time
+template<int L, bool WANT_H, bool IP>
+__global__ void __launch_bounds__(32 * kCoopMaxWarps) gerg_iso_coop_kernel(const double* __restrict__ blob_g, const int blob_words, const int rows,
+                                                                             const double Rgas, const DeviceBatch in, const IsochoricOut o,
+                                                                             const IsoPropsOut ip) {
+    extern __shared__ double sm[];
+    for (int i = threadIdx.x; i < blob_words; i += blockDim.x) sm[i] = __ldg(blob_g + i);
+    __syncthreads();
+    constexpr int PPW = 32 / L;
+    const int warp = threadIdx.x >> 5, l32 = threadIdx.x & 31;
+    const int grp = l32 / L, lane = l32 % L;
+    const int wpc = blockDim.x >> 5;
+    double* W = sm + blob_words + (size_t)warp * rows * PPW + grp;
+    const int nc = reinterpret_cast<const GergIsoHdr*>(sm)->nc;
+    const long long stride = (long long)gridDim.x * wpc * PPW;
+    for (long long base = ((long long)blockIdx.x * wpc + warp) * PPW; base < in.npts; base += stride) {
+        const long long k0 = base + grp;
+        const bool valid = k0 < in.npts;
+        const long long k = valid ? k0 : in.npts - 1;
+        for (int i = lane; i < nc; i += L) W[i * PPW] = __ldg(in.x + (long long)i * in.x_stride + k);
+        __syncwarp();
+        gerg_iso_coop_point<L, WANT_H>(sm, Rgas, __ldg(in.T + k), W, PPW, lane, valid, o, k, in.npts, IP ? &ip : nullptr);
+        __syncwarp();
+    }
+}
+
+template<int L, bool WANT_H, bool IP>
+bool coop_launch_l(const double* blob_d, const GergIsoHdr& h, double Rgas, const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip,
+                   cudaStream_t st) {
+    constexpr int PPW = 32 / L;
+    const int rows = gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, WANT_H);
+    const size_t blob_bytes = (size_t)h.nwords * 8, per_warp = (size_t)rows * PPW * 8;
+    if (blob_bytes + 2 * per_warp + 1024 > kSmemPerSM) return false;
+    int nwarps = (int)std::min<size_t>(kCoopMaxWarps, (kSmemPerSM - 1024 - blob_bytes) / per_warp);
+    if (const char* e = std::getenv("TEQPB200_ISO_COOP_WARPS")) nwarps = std::max(1, std::min(nwarps, std::atoi(e)));
+    const size_t smem = blob_bytes + per_warp * nwarps;
+    auto kern = gerg_iso_coop_kernel<L, WANT_H, IP>;
+    if (smem > 48 * 1024) TQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long per_cta = (long long)nwarps * PPW;
+    const int grid = (int)std::min<long long>(sm_count(), (in.npts + per_cta - 1) / per_cta);
+    kern<<<grid, 32 * nwarps, smem, st>>>(blob_d, h.nwords, rows, Rgas, in, o, ip);
+    TQ_CUDA(cudaGetLastError());
+    return true;
+}
+
+template<bool WANT_H, bool IP>
+bool coop_launch(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o,
+                 const IsoPropsOut& ip, cudaStream_t st) {
+    static const int L = [] { const char* e = std::getenv("TEQPB200_ISO_COOP_L"); return e ? std::atoi(e) : 8; }();
+    if (L == 0) return false;   // TEQPB200_ISO_COOP_L=0: the thread-per-point kernels (A/B measurements)
+    int dev = 0;
+    TQ_CUDA(cudaGetDevice(&dev));
+    const double* blob_d = tab.on_device(P, dev);
+    const GergIsoHdr& h = *reinterpret_cast<const GergIsoHdr*>(tab.host.data());
+    if (L == 4) return coop_launch_l<4, WANT_H, IP>(blob_d, h, Rgas, in, o, ip, st);
+    if (L == 16) return coop_launch_l<16, WANT_H, IP>(blob_d, h, Rgas, in, o, ip, st);
+    return coop_launch_l<8, WANT_H, IP>(blob_d, h, Rgas, in, o, ip, st);
+}
+
+}  // namespace
+
+const double* GergIsoDeviceTables::on_device(const GergProgram& P, int dev) const {
+    std::lock_guard<std::mutex> g(mtx_);
+    if (host.empty()) const_cast<std::vector<double>&>(host) = gerg_iso_build_blob(P);
+    auto it = dev_.find(dev);
+    if (it != dev_.end()) return it->second;
+    double* d = nullptr;
+    TQ_CUDA(cudaMalloc(&d, host.size() * sizeof(double)));
+    TQ_CUDA(cudaMemcpy(d, host.data(), host.size() * sizeof(double), cudaMemcpyHostToDevice));
+    dev_[dev] = d;
+    return d;
+}
+GergIsoDeviceTables::~GergIsoDeviceTables() {
+    for (auto& kv : dev_) cudaFree(kv.second);
+}
+
+bool gerg_coop_launch_isochoric(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o,
+                                cudaStream_t st) {
+    if (in.npts == 0) return true;
+    const IsoPropsOut none{};
+    return o.hess ? coop_launch<true, false>(tab, P, Rgas, in, o, none, st) : coop_launch<false, false>(tab, P, Rgas, in, o, none, st);
+}
+bool gerg_coop_launch_isoprops(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& ip,
+                               cudaStream_t st) {
+    if (in.npts == 0) return true;
+    const IsochoricOut none{};
+    return coop_launch<true, true>(tab, P, Rgas, in, none, ip, st);
+}
 
 void gerg_launch_isoprops(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& ip, cudaStream_t st) {
     if (in.npts == 0) return;

@@ -4,6 +4,7 @@
 // in a plain host loop, on the very parameter block the product's JSON ingestion builds.  Purpose: the build container has no
 // GPU, so this lets the CPU-only test tier (-m "not gpu") check the kernels' MATHEMATICS against the oracle before a GPU box is
 // spent on them.  The GPU parity tests (-m gpu) go through the C ABI of libteqpb200.so and do not touch this file.
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -14,6 +15,7 @@
 #include "../../teqp_b200/csrc/tq_generic_dir.cuh"
 #include "../../teqp_b200/csrc/tq_gerg.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_iso.cuh"
+#include "../../teqp_b200/csrc/tq_gerg_iso_coop.cuh"
 #include "../../teqp_b200/csrc/tq_gerg_jet.cuh"
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
 #include "../../teqp_b200/csrc/tq_assoc.cuh"
@@ -105,7 +107,20 @@ void generic_iso(const typename M::Params& p, int nc, long long npts, const doub
         generic_isochoric_point<M, M::kMaxC>(p, nc, T[k], r, o, k, npts);
     }
 }
+// the product launches the lane-cooperative form (tq_gerg_iso_coop.cuh) unless TEQPB200_ISO_COOP_L=0; one lane plays all the lanes here
+bool coop_off() { const char* e = std::getenv("TEQPB200_ISO_COOP_L"); return e && std::atoi(e) == 0; }
 void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const double* T, const double* rv, const IsochoricOut& o) {
+    if (!coop_off()) {
+        const std::vector<double> blob = gerg_iso_build_blob(P);
+        const GergIsoHdr& h = *reinterpret_cast<const GergIsoHdr*>(blob.data());
+        std::vector<double> W((size_t)gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, true));
+        for (long long k = 0; k < npts; ++k) {
+            for (int i = 0; i < P.nc; ++i) W[(size_t)i] = rv[(long long)i * npts + k];
+            if (o.hess) gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, o, k, npts);
+            else gerg_iso_coop_point<1, false>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, o, k, npts);
+        }
+        return;
+    }
     constexpr int WS = 32;
     const Exp2K K = Exp2K::load();
     std::vector<double> W((size_t)gerg_iso_rows(P.nc, P.nw, true) * WS);
@@ -116,10 +131,20 @@ void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const doub
     }
 }
 void gerg_ip_loop(const GergProgram& P, double Rgas, long long npts, const double* T, const double* rv, const IsoPropsOut& ip) {
+    const IsochoricOut none{};
+    if (!coop_off()) {
+        const std::vector<double> blob = gerg_iso_build_blob(P);
+        const GergIsoHdr& h = *reinterpret_cast<const GergIsoHdr*>(blob.data());
+        std::vector<double> W((size_t)gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, true));
+        for (long long k = 0; k < npts; ++k) {
+            for (int i = 0; i < P.nc; ++i) W[(size_t)i] = rv[(long long)i * npts + k];
+            gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, none, k, npts, &ip);
+        }
+        return;
+    }
     constexpr int WS = 32;
     const Exp2K K = Exp2K::load();
     std::vector<double> W((size_t)gerg_iso_rows(P.nc, P.nw, true) * WS);
-    const IsochoricOut none{};
     for (long long k = 0; k < npts; ++k) {
         for (int i = 0; i < P.nc; ++i) W[(size_t)i * WS] = rv[(long long)i * npts + k];
         gerg_iso_point<WS, true>(P, K, Rgas, T[k], W.data(), none, k, npts, &ip);
