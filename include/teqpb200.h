@@ -124,6 +124,21 @@ void* teqpb200_host_alloc(unsigned long long nbytes);       /* pinned host memor
 void teqpb200_host_free(void* p);
 long long int teqpb200_kernel_launches(void);               /* kernels launched by this library so far (all threads) */
 int teqpb200_release_scratch(void);                         /* frees the device staging arenas of the host-pointer path */
+/* ---- no-allocation variant of get_Arxy_batch.  NO COUNTERPART IN THE REFERENCE: added for callers
+   that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arguments, results and pair rules as
+   get_Arxy_batch, TEQPB200_DEVICE_PTRS only (stream of teqpb200_set_stream), npairs <= 32.  The covering derivative table is kept in a static
+   device array of teqpb200_noalloc_max_doubles() = 4 Mi doubles (32 MiB per GPU that loads the library, held until exit) instead of a
+   cudaMallocAsync block: a call needing more than that many (scratch rows x npts) doubles is rejected with an error (code 1) -- split the batch.
+   The call makes no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library routine; for families whose kernels are generated
+   per model (GERG, multifluid) the shape must have been used once through get_Arxy_batch / get_Ar0n_batch before (otherwise: error, not a
+   compile).  All calls share the one array: calls that overlap on the GPU (other streams, other host threads) race on it.
+   teqpb200_noalloc_setup() resolves the array's device address for the CURRENT device (once per device; the entry point does it at first use
+   otherwise). */
+int get_Arxy_batch_noalloc(const long long int uuid, const int npairs, const int* NT, const int* ND, const long long int npts,
+                           const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out, const int flags,
+                           char* errmsg, int errmsg_length);
+long long int teqpb200_noalloc_max_doubles(void);
+int teqpb200_noalloc_setup(char* errmsg, int errmsg_length);
 void teqpb200_inject_fault(const long long int chunk_index); /* TEST HOOK: the chunk_index-th staged chunk from now on fails (error-path tests) */
 double teqpb200_last_call_device_ms(const int device);      /* device-side duration (first H2D .. last D2H, CUDA events) of the last
                                                                host-pointer call on that device; -1 if none */

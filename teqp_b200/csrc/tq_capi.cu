@@ -877,3 +877,113 @@ extern "C" int teqpb200_fp64_peak(double* tflops, char* errmsg, int errmsg_lengt
         *tflops = best;
     });
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// No-allocation variant of get_Arxy_batch (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  get_Arxy_batch evaluates the covering sweeps into a device
+// scratch table it obtains from cudaMallocAsync and gathers the requested rows from it; here the scratch table is a file-scope device
+// array of kNoAllocMaxDoubles doubles (32 MiB, held by every GPU that loads the library until the process exits).  The array's name
+// is a host-side stand-in in host code: its device address is resolved once per device with cudaGetSymbolAddress and passed on.
+// Every call shares the array (the sweeps overwrite every scratch row they use before it is read, so nothing has to be cleared);
+// calls that overlap on the GPU -- different streams, different host threads -- race on it.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr long long kNoAllocMaxDoubles = 4ll << 20;
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocMaxDoubles];
+
+namespace {
+constexpr int kNoAllocMaxPairs = 32;
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mtx;
+double* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+struct NoAllocGather { int npairs; int src_row[kNoAllocMaxPairs]; };
+
+// out[p][k] = scratch[src_row[p]][k]; scratch is the DEVICE address of g_noalloc_scratch (from cudaGetSymbolAddress)
+__global__ void noalloc_gather_kernel(const double* __restrict__ scratch, const NoAllocGather g, const long long npts, double* __restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride)
+        for (int p = 0; p < g.npairs; ++p) out[(long long)p * npts + k] = scratch[(long long)g.src_row[p] * npts + k];
+}
+
+// device address of the scratch array on the CURRENT device (resolved once per device, with that device current)
+double* noalloc_scratch_ptr() {
+    int dev = 0;
+    TQ_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) throw InvalidArgument("device ordinal out of range for the no-allocation entry point");
+    std::lock_guard<std::mutex> g(g_noalloc_mtx);
+    if (!g_noalloc_ptr[dev]) {
+        double* p = nullptr;
+        TQ_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) throw std::runtime_error("cudaGetSymbolAddress returned a null address for the no-allocation scratch array");
+        g_noalloc_ptr[dev] = p;
+    }
+    return g_noalloc_ptr[dev];
+}
+}  // namespace
+
+extern "C" {
+
+long long int teqpb200_noalloc_max_doubles(void) { return kNoAllocMaxDoubles; }
+
+int teqpb200_noalloc_setup(char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] { (void)noalloc_scratch_ptr(); });
+}
+
+int get_Arxy_batch_noalloc(const long long int uuid, const int npairs, const int* NT, const int* ND, const long long int npts,
+                           const double* T, const double* rho, const double* molefrac, const int Ncomp, double* out, const int flags,
+                           char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (!(flags & TEQPB200_DEVICE_PTRS)) throw InvalidArgument("get_Arxy_batch_noalloc takes device pointers only (TEQPB200_DEVICE_PTRS)");
+        if (npairs <= 0 || npairs > kNoAllocMaxPairs) throw InvalidArgument("npairs must be in 1.." + std::to_string(kNoAllocMaxPairs));
+        if (npts < 0) throw InvalidArgument("npts must be non-negative");
+        if (npts == 0) return;
+        // same partition of the pairs over the compiled sweeps as get_Arxy_batch (row NT = 0, column ND = 0, block NT <= 2, ND <= 4)
+        int rowND = -1, colNT = -1, blkNT = -1, blkND = -1;
+        int where[kNoAllocMaxPairs];
+        for (int p = 0; p < npairs; ++p) {
+            const int nt = NT[p], nd = ND[p];
+            if (nt < 0 || nd < 0 || nt > kMaxDerivT || nd > kMaxDerivD) throw InvalidArgument("derivative order out of range");
+            if (nt == 0) where[p] = 0;
+            else if (nd == 0) where[p] = 1;
+            else if (nt <= 2 && nd <= 4) { where[p] = 2; blkNT = std::max(blkNT, nt); blkND = std::max(blkND, nd); }
+            else throw InvalidArgument("mixed derivative (" + std::to_string(nt) + "," + std::to_string(nd) + ") is outside the compiled sweeps: NT = 0 with ND <= 6, ND = 0 with NT <= 4, or NT <= 2 with ND <= 4");
+        }
+        for (int p = 0; p < npairs; ++p) {
+            if (blkNT >= 0 && where[p] == 0 && ND[p] <= 4) { where[p] = 2; blkND = std::max(blkND, ND[p]); }
+            else if (blkNT >= 0 && where[p] == 1 && NT[p] <= 2) { where[p] = 2; blkNT = std::max(blkNT, NT[p]); }
+        }
+        for (int p = 0; p < npairs; ++p) {
+            if (where[p] == 0) rowND = std::max(rowND, ND[p]);
+            if (where[p] == 1) colNT = std::max(colNT, NT[p]);
+        }
+        const int rows_row = rowND >= 0 ? rowND + 1 : 0, rows_col = colNT >= 0 ? colNT + 1 : 0, rows_blk = blkNT >= 0 ? (blkNT + 1) * (blkND + 1) : 0;
+        const long long rows = rows_row + rows_col + rows_blk;
+        if (rows * npts > kNoAllocMaxDoubles)
+            throw InvalidArgument("get_Arxy_batch_noalloc: " + std::to_string(rows) + " scratch rows x " + std::to_string(npts) + " points exceed the static scratch array of " +
+                                  std::to_string(kNoAllocMaxDoubles) + " doubles; split the batch or call get_Arxy_batch");
+        // per-model generated kernels are compiled and loaded (which allocates) at the first use of a shape: refuse rather than allocate
+        if ((rows_row && !m->ar_table_ready(0, rowND)) || (rows_col && !m->ar_table_ready(colNT, 0)) || (rows_blk && !m->ar_table_ready(blkNT, blkND)))
+            throw InvalidArgument("get_Arxy_batch_noalloc: this model's kernel for the requested shape has not been generated yet; call get_Arxy_batch once with the same pairs first");
+        double* const scratch = noalloc_scratch_ptr();
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        const DeviceBatch b = make_batch(npts, T, rho, molefrac, bc);
+        double* srow = scratch;
+        double* scol = srow + (size_t)rows_row * npts;
+        double* sblk = scol + (size_t)rows_col * npts;
+        cudaStream_t st = tl_stream;
+        if (rows_row) { m->launch_ar_table(0, rowND, b, srow, st); ++g_launches; }
+        if (rows_col) { m->launch_ar_table(colNT, 0, b, scol, st); ++g_launches; }
+        if (rows_blk) { m->launch_ar_table(blkNT, blkND, b, sblk, st); ++g_launches; }
+        NoAllocGather g{};
+        g.npairs = npairs;
+        for (int p = 0; p < npairs; ++p)
+            g.src_row[p] = where[p] == 0 ? ND[p] : where[p] == 1 ? rows_row + NT[p] : rows_row + rows_col + NT[p] * (blkND + 1) + ND[p];
+        noalloc_gather_kernel<<<grid_for(npts, 256, 8 * sm_count()), 256, 0, st>>>(scratch, g, npts, out);
+        TQ_CUDA(cudaGetLastError());
+        ++g_launches;
+    });
+}
+
+}  // extern "C"
