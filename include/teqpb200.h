@@ -112,6 +112,29 @@ int get_dmBnvirdTm_batch(const long long int uuid, const int Nvir, const int NT,
 int get_Psir_sigma_derivs_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const double* v,
                                 const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);
 
+/* Batched caller of the hot path: teqp::pure_VLE_T / AbstractModel::pure_VLE_T
+   (/root/reference/include/teqp/algorithms/VLE_pure.hpp:18-143; teqpcpp.hpp) for npts isotherms at once -- Newton's method on
+   p(T, rhoL) = p(T, rhoV), mu(T, rhoL) = mu(T, rhoV) from the guesses rhoL0[k], rhoV0[k], at most maxiter steps with the reference's stopping
+   rules per point, every iteration ONE launch of the Lambda table kernel over the 2 npts liquid + vapour densities and one update kernel, no
+   host round trip.  molefrac[Ncomp] is ONE composition for all points ([1.0] for a one-component model; a pure fluid inside a mixture model is
+   its unit vector), whatever the TEQPB200_BROADCAST_X flag says.  Optional outputs (NULL to skip): psat[k] = rhoV R T (1 + Ar01(rhoV)) and
+   dpsatdT[k] = teqp::dpsatdT_pure (VLE_pure.hpp:158-171, Clapeyron).  A point that does not converge returns whatever the iteration produced
+   (possibly the trivial solution rhoL = rhoV or non-finite values), as the reference does. */
+int pure_VLE_T_batch(const long long int uuid, const long long int npts, const double* T, const double* rhoL0, const double* rhoV0, const int maxiter,
+                     const double* molefrac, const int Ncomp, double* rhoL, double* rhoV, double* psat, double* dpsatdT, const int flags,
+                     char* errmsg, int errmsg_length);
+
+/* Per-point status of a finished batched call (the "per-point int* status" of SURVEY.md section 8b; the reference throws per call --
+   teqp::InvalidArgument / IterationFailure, /root/reference/include/teqp/exceptions.hpp:17-64 -- where a batch can only flag the point):
+   status[k] is a bit set computed on the GPU from the inputs of point k and the nrows output rows out[r][k] a previous entry point wrote for it
+   (nrows = 0: inputs only).  Failures inside the models (e.g. the Barker-Henderson diameter iteration of SAFT-VR-Mie, saftvrmie.hpp d > sigma / j < 1)
+   surface as non-finite outputs.  Same pointer / flag conventions as get_Ar0n_batch; status is int[npts] (a device pointer with TEQPB200_DEVICE_PTRS). */
+#define TEQPB200_STATUS_BAD_INPUT 1          /* T <= 0, rho < 0, a mole fraction < 0, or any of them not finite */
+#define TEQPB200_STATUS_NONFINITE_OUTPUT 2   /* an output row holds NaN / Inf at this point */
+#define TEQPB200_STATUS_COMPOSITION_SUM 4    /* |sum(x) - 1| > 1e-6 (informational: the reference does not normalise or check) */
+int teqpb200_point_status_batch(const long long int uuid, const long long int npts, const double* T, const double* rho, const double* molefrac,
+                                const int Ncomp, const int nrows, const double* out, int* status, const int flags, char* errmsg, int errmsg_length);
+
 /* ---------------- utilities ---------------- */
 /* AbstractModel::get_reducing_temperature (which = 0) / get_reducing_density (which = 1), teqpcpp.hpp:124-125: multi-fluid families only */
 int teqpb200_get_reducing(const long long int uuid, const int which, const double* molefrac, const int Ncomp, double* val, char* errmsg, int errmsg_length);

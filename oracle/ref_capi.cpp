@@ -18,6 +18,8 @@
 #include "teqp/models/GERG/GERG.hpp"
 #include "teqp/models/pcsaft.hpp"
 #include "teqp/models/multifluid.hpp"
+#include "teqp/ideal_eosterms.hpp"
+#include "teqp/algorithms/VLE_pure.hpp"
 
 #include <thread>
 #include <vector>
@@ -33,6 +35,9 @@ namespace teqp { namespace cppinterface {
     std::unique_ptr<AbstractModel> make_GERG2004resid(const nlohmann::json &);
     std::unique_ptr<AbstractModel> make_GERG2008resid(const nlohmann::json &);
     std::unique_ptr<AbstractModel> make_multifluid(const nlohmann::json &);   // interface/CPP/model_factory_multifluid.cpp
+    std::unique_ptr<AbstractModel> make_GERG2004idealgas(const nlohmann::json &);   // interface/CPP/model_factory_GERG.cpp:19-24
+    std::unique_ptr<AbstractModel> make_GERG2008idealgas(const nlohmann::json &);
+    std::unique_ptr<AbstractModel> make_IdealHelmholtz(const nlohmann::json &);     // interface/CPP/model_factory_IdealHelmholtz.cpp
 }}
 
 using namespace teqp;
@@ -60,6 +65,9 @@ std::unique_ptr<AbstractModel> build(const nlohmann::json& j, std::string& kind)
     if (kind == "GERG2004resid") return make_GERG2004resid(spec);
     if (kind == "GERG2008resid") return make_GERG2008resid(spec);
     if (kind == "multifluid") return make_multifluid(spec);
+    if (kind == "GERG2004idealgas") return make_GERG2004idealgas(spec);
+    if (kind == "GERG2008idealgas") return make_GERG2008idealgas(spec);
+    if (kind == "IdealHelmholtz") return make_IdealHelmholtz(spec);
     throw std::invalid_argument("Don't understand \"kind\" of: " + kind);
 }
 
@@ -304,6 +312,9 @@ int ref_lnphi_family(void* h, int what, long long npts, const double* T, const d
     else if (rm->kind == "PR" || rm->kind == "SRK" || rm->kind == "cubic") { using M = decltype(make_canonicalPR(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "PCSAFT") { using M = decltype(PCSAFT::PCSAFTfactory(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "multifluid") { using M = decltype(multifluidfactory(nlohmann::json{})); const auto& m = get_model_cref<M>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "GERG2008idealgas") { const auto& m = get_model_cref<GERG2008::GERG2008IdealGasModel>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "GERG2004idealgas") { const auto& m = get_model_cref<GERG2004::GERG2004IdealGasModel>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "IdealHelmholtz") { const auto& m = get_model_cref<IdealHelmholtz>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else { put_err("ln(phi) family: kind not wired in the oracle: " + rm->kind, err, errlen); return 200; }
     return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
         thread_local Eigen::ArrayXd r, v; if (r.size() != ncomp) r.resize(ncomp);
@@ -371,6 +382,19 @@ int ref_get_Ataudelta(void* h, int which, int Ntau, int Ndelta, const int* idx, 
         if (which == 1) out[k] = am.get_AtaudeltaXi(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1]);
         else if (which == 2) out[k] = am.get_AtaudeltaXiXj(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1], idx[2], idx[3]);
         else out[k] = am.get_AtaudeltaXiXjXk(tau[k], Ntau, delta[k], Ndelta, z, idx[0], idx[1], idx[2], idx[3], idx[4], idx[5]);
+    });
+}
+// teqp::pure_VLE_T and teqp::dpsatdT_pure (algorithms/VLE_pure.hpp:138-171; what AbstractModel::pure_VLE_T / dpsatdT_pure forward to,
+// AbstractModel_implementation.cpp) per isotherm; z = one composition for all points; psat from the vapour density
+int ref_pure_VLE_T(void* h, long long npts, const double* T, const double* rhoL0, const double* rhoV0, int maxiter, const double* z, int ncomp,
+                   double* rhoL, double* rhoV, double* psat, double* dpsatdT, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    const Eigen::ArrayXd zz = Eigen::Map<const Eigen::ArrayXd>(z, ncomp);
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        const auto r = teqp::pure_VLE_T(am, T[k], rhoL0[k], rhoV0[k], maxiter, zz);
+        rhoL[k] = r[0]; rhoV[k] = r[1];
+        if (psat) psat[k] = r[1] * am.get_R(zz) * T[k] * (1.0 + am.get_Ar01(T[k], r[1], zz));
+        if (dpsatdT) dpsatdT[k] = teqp::dpsatdT_pure(am, T[k], r[0], r[1], zz);
     });
 }
 } // extern "C"

@@ -10,6 +10,7 @@
 #include <unordered_map>
 
 #include "../../include/teqpb200.h"
+#include "tq_vle.cuh"
 #include "tq_common.hpp"
 
 namespace tq {
@@ -25,6 +26,10 @@ int sm_count() {
     return n;
 }
 
+// ideal-gas kinds (tq_ideal.cu)
+std::unique_ptr<Model> make_ideal_helmholtz_model(const Json& jpures);
+std::unique_ptr<Model> make_gerg_idealgas_model(const std::string& kind, const Json& spec);
+
 std::unique_ptr<Model> make_model(const Json& j) {
     // kind -> factory; the in-scope subset of /root/reference/interface/CPP/teqp_impl_factory.cpp:54-102
     const std::string kind = j.at("kind").as_string();
@@ -36,6 +41,8 @@ std::unique_ptr<Model> make_model(const Json& j) {
     if (kind == "SAFT-VR-Mie") return make_saftvrmie_model(spec);
     if (kind == "genericSAFT") return make_genericsaft_model(spec);
     if (kind == "multifluid") return make_multifluid_model(spec);
+    if (kind == "IdealHelmholtz") return make_ideal_helmholtz_model(spec);
+    if (kind == "GERG2008idealgas" || kind == "GERG2004idealgas") return make_gerg_idealgas_model(kind, spec);
     throw InvalidArgument("Don't understand \"kind\" of: " + kind);
 }
 
@@ -270,6 +277,30 @@ void ar_table_call(const Model& m, int NT, int ND, long long npts, const double*
             m.launch_ar_table(NT, ND, make_batch(n, din[0], din[1], din[2], bc), dout[0], st);
             ++g_launches;
         });
+}
+
+
+// per-point status (SURVEY 8b "per-point int* status optional"): classifies each point of a finished batched call from its inputs and outputs
+template<class OutT>
+__global__ void __launch_bounds__(256) point_status_kernel(const DeviceBatch in, const int nc, const double* __restrict__ out, const int nrows,
+                                                            OutT* __restrict__ status) {
+    const long long npts = in.npts;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < npts; k += stride) {
+        int s = 0;
+        const double T = __ldg(in.T + k), rho = __ldg(in.rho + k);
+        if (!(T > 0) || !isfinite(T) || !(rho >= 0) || !isfinite(rho)) s |= TEQPB200_STATUS_BAD_INPUT;
+        double sum = 0.0;
+        for (int i = 0; i < nc; ++i) {
+            const double x = __ldg(in.x + (long long)i * in.x_stride + (in.x_bcast ? 0 : k));
+            if (!(x >= 0) || !isfinite(x)) s |= TEQPB200_STATUS_BAD_INPUT;
+            sum += x;
+        }
+        if (!(fabs(sum - 1.0) <= 1e-6)) s |= TEQPB200_STATUS_COMPOSITION_SUM;
+        for (int r = 0; r < nrows; ++r)
+            if (!isfinite(__ldg(out + (long long)r * npts + k))) s |= TEQPB200_STATUS_NONFINITE_OUTPUT;
+        status[k] = (OutT)s;
+    }
 }
 
 }  // namespace
@@ -696,6 +727,83 @@ int get_Psir_sigma_derivs_batch(const long long int uuid, const long long int np
                 m->launch_sigma_derivs(make_batch(n, din[0], nullptr, din[1], false), din[2], dout[0], st);
                 ++g_launches;
             });
+    });
+}
+
+int pure_VLE_T_batch(const long long int uuid, const long long int npts, const double* T, const double* rhoL0, const double* rhoV0, const int maxiter,
+                     const double* molefrac, const int Ncomp, double* rhoL, double* rhoV, double* psat, double* dpsatdT, const int flags,
+                     char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (maxiter < 0) throw InvalidArgument("maxiter must be non-negative");
+        if (!molefrac) throw InvalidArgument("molefrac must be given ([1.0] for a one-component model)");
+        if (!rhoL || !rhoV) throw InvalidArgument("rhoL and rhoV must not be null");
+        const bool want_extra = psat || dpsatdT;
+        double R = 0.0;
+        if (want_extra) {   // AbstractModel::get_R(molefrac) on the host (VLE_pure.hpp:163): the composition is one Ncomp-vector
+            std::vector<double> xh((size_t)Ncomp);
+            if (flags & TEQPB200_DEVICE_PTRS) {
+                TQ_CUDA(cudaMemcpyAsync(xh.data(), molefrac, sizeof(double) * Ncomp, cudaMemcpyDeviceToHost, tl_stream));
+                TQ_CUDA(cudaStreamSynchronize(tl_stream));
+            } else {
+                for (int i = 0; i < Ncomp; ++i) xh[i] = molefrac[i];
+            }
+            R = m->R(xh.data(), Ncomp);
+        }
+        // scratch rows (device only): T2[2], rho2[2], done[1], A[3][2], B[4][2]
+        run(flags, npts, {{T, 1, false}, {rhoL0, 1, false}, {rhoV0, 1, false}, {molefrac, Ncomp, true}},
+            {{rhoL, 1}, {rhoV, 1}, {psat, 1}, {dpsatdT, 1}, {nullptr, 2}, {nullptr, 2}, {nullptr, 1}, {nullptr, 6}, {nullptr, want_extra ? 8 : 1}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                double *T2 = dout[4], *rho2 = dout[5], *done = dout[6], *A = dout[7], *B = dout[8];
+                const int grid = grid_for(n, 256, sm_count() * 8);
+                pure_vle_init_kernel<<<grid, 256, 0, st>>>(n, din[0], din[1], din[2], T2, rho2, done);
+                TQ_CUDA(cudaGetLastError());
+                ++g_launches;
+                const DeviceBatch b2 = make_batch(2 * n, T2, rho2, din[3], true);
+                for (int it = 0; it < maxiter; ++it) {
+                    m->launch_ar_table(0, 2, b2, A, st);
+                    pure_vle_update_kernel<<<grid, 256, 0, st>>>(n, A, rho2, done);
+                    TQ_CUDA(cudaGetLastError());
+                    g_launches += 2;
+                }
+                if (want_extra) { m->launch_ar_table(1, 1, b2, B, st); ++g_launches; }
+                pure_vle_finish_kernel<<<grid, 256, 0, st>>>(n, din[0], rho2, want_extra ? B : nullptr, R, dout[0], dout[1], psat ? dout[2] : nullptr,
+                                                             dpsatdT ? dout[3] : nullptr);
+                TQ_CUDA(cudaGetLastError());
+                ++g_launches;
+            });
+    });
+}
+
+int teqpb200_point_status_batch(const long long int uuid, const long long int npts, const double* T, const double* rho, const double* molefrac,
+                                const int Ncomp, const int nrows, const double* out, int* status, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (nrows < 0 || (nrows > 0 && !out)) throw InvalidArgument("nrows must be non-negative and out non-null when nrows > 0");
+        if (!status) throw InvalidArgument("status must not be null");
+        if (npts < 0) throw InvalidArgument("npts must be non-negative");
+        if (npts == 0) return;
+        const bool bc = flags & TEQPB200_BROADCAST_X;
+        if (flags & TEQPB200_DEVICE_PTRS) {
+            point_status_kernel<int><<<grid_for(npts, 256, sm_count() * 8), 256, 0, tl_stream>>>(make_batch(npts, T, rho, molefrac, bc), Ncomp, out, nrows, status);
+            TQ_CUDA(cudaGetLastError());
+            ++g_launches;
+            return;
+        }
+        // host buffers: the staging pipeline moves rows of doubles, so the status row is staged as doubles and narrowed on the host
+        std::vector<double> tmp((size_t)npts);
+        std::vector<HostIn> ins = {{T, 1, false}, {rho, 1, false}, {molefrac, Ncomp, bc}};
+        if (nrows > 0) ins.push_back({out, nrows, false});
+        run_host(npts, ins, {{tmp.data(), 1}},
+                 [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                     point_status_kernel<double><<<grid_for(n, 256, sm_count() * 8), 256, 0, st>>>(make_batch(n, din[0], din[1], din[2], bc), Ncomp,
+                                                                                                   nrows > 0 ? din[3] : nullptr, nrows, dout[0]);
+                     TQ_CUDA(cudaGetLastError());
+                     ++g_launches;
+                 });
+        for (long long k = 0; k < npts; ++k) status[k] = (int)tmp[(size_t)k];
     });
 }
 

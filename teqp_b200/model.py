@@ -229,6 +229,51 @@ class Model:
                                                  err, C.c_int(2000)), err)
         return ao.obj
 
+    def pure_VLE_T_batch(self, T, rhoL0, rhoV0, maxiter=10, molefrac=None, want_extra=True):
+        """teqp::pure_VLE_T (algorithms/VLE_pure.hpp:108-143) for many isotherms at once: returns (rhoL, rhoV, psat, dpsatdT), the last two None
+        unless want_extra (dpsatdT as teqp::dpsatdT_pure, :158-171).  molefrac: ONE composition for all points (default [1.0])."""
+        dev = _is_torch(T)
+        flags = (DEVICE_PTRS if dev else 0) | BROADCAST_X
+        n = int(T.numel() if dev else np.size(T))
+        if molefrac is None:
+            molefrac = np.ones(1)
+        if dev and not _is_torch(molefrac):
+            import torch
+            molefrac = torch.as_tensor(np.ascontiguousarray(molefrac, dtype=np.float64), device=T.device)
+        aT, aL, aV, ax = _Arg(T, dev), _Arg(rhoL0, dev), _Arg(rhoV0, dev), _Arg(molefrac, dev)
+        nc = int(ax.obj.numel() if dev else ax.obj.size)
+        outs = [_Arg(self._out((n,), dev, T), dev) for _ in range(4 if want_extra else 2)]
+        null = C.cast(None, _dp)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().pure_VLE_T_batch(self._uuid, C.c_longlong(n), aT.ptr, aL.ptr, aV.ptr, C.c_int(maxiter), ax.ptr, C.c_int(nc), outs[0].ptr, outs[1].ptr,
+                                      outs[2].ptr if want_extra else null, outs[3].ptr if want_extra else null, C.c_int(flags), err, C.c_int(2000)), err)
+        return outs[0].obj, outs[1].obj, (outs[2].obj if want_extra else None), (outs[3].obj if want_extra else None)
+
+    def point_status_batch(self, T, rho, x, out=None):
+        """int32 [npts] bit set per point (teqpb200.h: 1 bad input, 2 non-finite output, 4 mole fractions do not sum to one) for the inputs of a
+        batched call and, if given, the [rows][npts] (or [..., npts]) output array it wrote -- the per-point counterpart of the exceptions the
+        reference throws per call"""
+        dev, flags, n, nc, aT, ar, ax = self._prep(T, rho, x)
+        nrows = 0
+        optr = None
+        if out is not None:
+            ao = _Arg(out.reshape(-1, n), dev)
+            nrows = int(ao.obj.shape[0])
+            optr = ao.ptr
+        if dev:
+            import torch
+            st = torch.empty(n, dtype=torch.int32, device=T.device)
+            sp = C.cast(C.c_void_p(st.data_ptr()), _ip)
+        else:
+            st = np.empty(n, dtype=np.int32)
+            sp = st.ctypes.data_as(_ip)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().teqpb200_point_status_batch(self._uuid, C.c_longlong(n), aT.ptr, ar.ptr, ax.ptr, C.c_int(nc), C.c_int(nrows), optr, sp,
+                                                 C.c_int(flags), err, C.c_int(2000)), err)
+        return st
+
     def get_reducing_temperature(self, molefrac):
         return self._reducing(0, molefrac)
 

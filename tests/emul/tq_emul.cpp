@@ -19,6 +19,8 @@
 #include "../../teqp_b200/csrc/tq_gerg_jet.cuh"
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
 #include "../../teqp_b200/csrc/tq_assoc.cuh"
+#include "../../teqp_b200/csrc/tq_ideal.cuh"
+#include "../../teqp_b200/csrc/tq_vle.cuh"
 
 using namespace tq;
 
@@ -223,6 +225,11 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             generic_table<GsaftDev>(p, p.mie.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
         }
+        if (fam == "idealgas") {
+            const IdealParams& p = *static_cast<const IdealParams*>(blob);
+            generic_table<IdealDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
 }
@@ -243,6 +250,7 @@ int emul_extras(const char* json, int what, int NT, int ND, long long npts, cons
         if (fam == "cubic" || fam == "vdW") TQ_FAM(CubicDev, CubicParams, p.nc)
         if (fam == "PCSAFT") TQ_FAM(PcsaftDev, PcsaftParams, p.nc)
         if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") TQ_FAM(GsaftDev, GsaftParams, p.mie.nc)
+        if (fam == "idealgas" && what == 1) TQ_FAM(IdealDev, IdealParams, p.nc)
 #undef TQ_FAM
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -275,6 +283,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_atrhoxi<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "idealgas") generic_atrhoxi<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three small-jet parts the product launches for this family (GsaftModel::launch_ATrhoXi_table)
@@ -301,6 +310,7 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         const void* blob = m->params_blob(&nb);
         const std::string fam = m->family();
         if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "idealgas") generic_xx<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "PCSAFT") dir_xx<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") dir_xx<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
@@ -321,6 +331,7 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         o.pr = outs[0]; o.splus = outs[1]; o.dpdT = outs[2]; o.d2PsirdTdrhoi = outs[3]; o.dpdrhovec = outs[4]; o.pmv = outs[5];
         o.chempotVLE = outs[6]; o.dchempotdT = outs[7]; o.dlnphi_dT = outs[8]; o.dlnphi_drho = outs[9]; o.dlnphi_dv = outs[10]; o.dlnphi_dx = outs[11];
         if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "idealgas") generic_ip<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three single-shape parts the product launches for this family (GsaftModel::launch_isoprops)
@@ -356,6 +367,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         const std::string fam = m->family();
         IsochoricOut o; o.Psir = f; o.grad = g; o.hess = H; o.lnphi = lnphi; o.phi = phi;
         if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "idealgas") generic_iso<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
@@ -367,6 +379,18 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
+}
+
+// one Newton update of the batched pure-fluid saturation solver (pure_vle_update_kernel, tq_vle.cuh): A[3][2n], rho2[2n], done[n]
+int emul_pure_vle_update(long long n, const double* A, double* rho2, double* done) {
+    const long long n2 = 2 * n;
+    for (long long k = 0; k < n; ++k) {
+        if (done[k] != 0.0) continue;
+        double rL = rho2[k], rV = rho2[n + k];
+        if (pure_vle_newton_point(A[k], A[n2 + k], A[2 * n2 + k], A[n + k], A[n2 + n + k], A[2 * n2 + n + k], rL, rV)) done[k] = 1.0;
+        else { rho2[k] = rL; rho2[n + k] = rV; }
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -187,3 +187,10 @@ def jit_ar_table(spec, NT, ND, T, rho, x):
     out = np.empty(((NT + 1) * (ND + 1), n))
     lib_.tqj_host(_p(consts), C.c_longlong(n), _p(T), _p(rho), _p(x), C.c_longlong(1 if bc else n), C.c_int(1 if bc else 0), _p(out))
     return out.reshape(NT + 1, ND + 1, n)
+
+
+def pure_vle_update(A, rho2, done):
+    n = done.size
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    assert A.shape == (3, 2 * n) and rho2.shape == (2 * n,)
+    lib().emul_pure_vle_update(C.c_longlong(n), _p(A), _p(rho2), _p(done))

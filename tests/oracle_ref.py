@@ -170,6 +170,14 @@ class RefModel:
         self._call(lib().ref_Psir_sigma_derivs, C.c_longlong(n), _p(T), _p(rv), _p(vv), C.c_int(rv.shape[0]), _p(out))
         return out
 
+    def pure_VLE_T(self, T, rhoL0, rhoV0, maxiter, z):
+        """teqp::pure_VLE_T + dpsatdT_pure per isotherm: (rhoL, rhoV, psat, dpsatdT)"""
+        T, rhoL0, rhoV0, z = (np.ascontiguousarray(a, dtype=np.float64) for a in (T, rhoL0, rhoV0, z))
+        n = T.size
+        rL, rV, ps, dp = (np.empty(n) for _ in range(4))
+        self._call(lib().ref_pure_VLE_T, C.c_longlong(n), _p(T), _p(rhoL0), _p(rhoV0), C.c_int(maxiter), _p(z), C.c_int(z.size), _p(rL), _p(rV), _p(ps), _p(dp))
+        return rL, rV, ps, dp
+
     def deriv_mat2(self, T, rho, x):
         T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
         n = T.size; x = _soa(x, n)

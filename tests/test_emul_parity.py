@@ -2,6 +2,7 @@
 This checks the MATHEMATICS the GPU will execute (same source, same parameter blocks) where no GPU is available."""
 import pytest
 
+import cases
 import parity_suite as ps
 
 AR_CASES = ["PR1", "PR2k", "SRK3", "cubicTwuMC", "vdW1", "vdW2", "PCSAFT1", "PCSAFT2", "PCSAFT3k", "GERG10", "GERG21", "GERG2004_3", "GERG_H2O_CO2",
@@ -97,3 +98,19 @@ def test_multifluid_coolprop_composition_derivative(emul, oracle):
     got = b.Ataudelta_table(spec, tau, delta, z[:, None].copy())[0, 0, 0, 1, 0]
     assert abs(got - (-0.0435874)) < 5e-8
     assert abs(got - m.Ataudelta(1, 0, 0, (0, 1), tau, delta, z[:, None].copy())[0]) < 1e-14
+
+
+@pytest.mark.parametrize("name", cases.IG_CASES)
+def test_idealgas(emul, oracle, name):
+    """the ideal-gas kinds (IdealHelmholtz with all ten term types, GERG-2004 / GERG-2008 ideal parts)"""
+    ps.idealgas_suite(ps.EmulBackend(emul), oracle, name, n=300)
+
+
+def test_idealgas_reference_pins(emul):
+    ps.idealgas_pins(ps.EmulBackend(emul))
+
+
+@pytest.mark.parametrize("name", sorted(ps.VLE_CASES))
+def test_pure_vle(emul, oracle, name):
+    """SURVEY 8 row f1: the batched pure-fluid saturation solver against teqp::pure_VLE_T / dpsatdT_pure"""
+    assert ps.pure_vle(ps.EmulBackend(emul), oracle, name, n=64) > 0

@@ -299,3 +299,44 @@ def test_arxy_batch_mixed_axis_pair_lists(be, oracle, name):
     for bad in ([(3, 1)], [(1, 5)], [(0, 7)], [(5, 0)]):
         with pytest.raises(teqp_b200.TeqpError):
             m.get_Arxy_batch(bad, T, rho, x)
+
+
+@pytest.mark.parametrize("name", cases.IG_CASES)
+def test_idealgas(be, oracle, name):
+    """the ideal-gas kinds (IdealHelmholtz with all ten term types, GERG-2004 / GERG-2008 ideal parts)"""
+    ps.idealgas_suite(be, oracle, name, n=600)
+
+
+def test_idealgas_reference_pins(be):
+    ps.idealgas_pins(be)
+
+
+def test_point_status(be):
+    """per-point status: bad inputs and non-finite outputs are flagged per point, on host and on device pointers"""
+    import torch
+    spec, T, rho, x = cases.points("GERG10", 5000)
+    T = T.copy(); rho = rho.copy(); x = x.copy()
+    T[10] = -5.0; T[11] = np.nan; rho[20] = -1.0; x[3, 30] = np.nan; x[2, 40] = -0.1; x[:, 50] *= 1.01
+    m = be.model(spec)
+    out = m.get_Ar0n_batch(4, T, rho, x)
+    st = m.point_status_batch(T, rho, x, out)
+    assert st.dtype == np.int32 and st.shape == (5000,)
+    bad = np.zeros(5000, bool); bad[[10, 11, 20, 30, 40]] = True
+    assert np.array_equal((st & 1) != 0, bad)
+    assert np.array_equal((st & 2) != 0, ~np.all(np.isfinite(out), axis=0))
+    off = np.zeros(5000, bool); off[[30, 40, 50]] = True       # NaN and -0.1 move the sum as well
+    assert np.array_equal((st & 4) != 0, off)
+    assert (st[[10, 11, 30]] & 2).all()                          # log of a negative / NaN propagates: the kernels do not mask failures
+    good = ~(bad | off)
+    assert not st[good].any()
+    assert np.array_equal(m.point_status_batch(T, rho, x), st & ~2)          # inputs only
+    dT, dr, dx, do = (torch.from_numpy(a).cuda() for a in (T, rho, x, out))
+    sd = m.point_status_batch(dT, dr, dx, do)
+    torch.cuda.synchronize()
+    assert sd.dtype == torch.int32 and np.array_equal(sd.cpu().numpy(), st)
+
+
+@pytest.mark.parametrize("name", sorted(ps.VLE_CASES))
+def test_pure_vle(be, oracle, name):
+    """SURVEY 8 row f1: the batched pure-fluid saturation solver against teqp::pure_VLE_T / dpsatdT_pure"""
+    assert ps.pure_vle(be, oracle, name, n=2000) > 0
