@@ -9,6 +9,7 @@
 #include <set>
 
 #include "tq_assoc.cuh"
+#include "tq_pcassoc.cuh"
 #include <cstdlib>
 
 #include "tq_common.hpp"
@@ -31,6 +32,21 @@ void gsaft_launch_sigma(const GsaftParams&, const DeviceBatch&, const double*, d
 void gsaft_launch_ip_part0(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);   // tq_ip_gsaft_{L,C,X}.cu
 void gsaft_launch_ip_part1(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
 void gsaft_launch_ip_part2(const GsaftParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
+
+void fill_pcsaft(PcsaftParams&, const Json&);   // tq_pcsaft.cu
+// genericSAFT with a PC-SAFT non-polar term: tq_pcassoc_k{1,2,4}.cu, tq_ax_pcassoc_{0,1,2}.cu, tq_ip_pcassoc_{L,C,X}.cu, tq_xx_pcassoc_{2,3}.cu, tq_ex_pcassoc.cu
+void pcassoc_launch_ar_rho(const PcAssocParams&, int ND, const DeviceBatch&, double*, cudaStream_t);
+void pcassoc_launch_ar_mixed(const PcAssocParams&, int NT, int ND, const DeviceBatch&, double*, cudaStream_t);
+void pcassoc_launch_isochoric(const PcAssocParams&, const DeviceBatch&, const IsochoricOut&, cudaStream_t);
+void pcassoc_launch_ATrhoXi_part0(const PcAssocParams&, const DeviceBatch&, double*, cudaStream_t);
+void pcassoc_launch_ATrhoXi_part1(const PcAssocParams&, const DeviceBatch&, double*, cudaStream_t);
+void pcassoc_launch_ATrhoXi_part2(const PcAssocParams&, const DeviceBatch&, double*, cudaStream_t);
+void pcassoc_launch_cross2(const PcAssocParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
+void pcassoc_launch_cross3(const PcAssocParams&, const DeviceBatch&, int, int, int, double*, cudaStream_t);
+void pcassoc_launch_sigma(const PcAssocParams&, const DeviceBatch&, const double*, double*, cudaStream_t);
+void pcassoc_launch_ip_part0(const PcAssocParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
+void pcassoc_launch_ip_part1(const PcAssocParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
+void pcassoc_launch_ip_part2(const PcAssocParams&, const DeviceBatch&, const IsoPropsOut&, double*, const double*, cudaStream_t);
 
 namespace {
 
@@ -91,6 +107,49 @@ public:
             IsochoricOut io; io.hess = H;
             gsaft_launch_isochoric(p, in, io, st);
             gsaft_launch_ip_part2(p, in, o, Ls, H, st);
+            TQ_CUDA(cudaFreeAsync(H, st));
+        }
+        TQ_CUDA(cudaFreeAsync(Ls, st));
+    }
+};
+
+// genericSAFT whose non-polar term is PC-SAFT (genericsaft.hpp:26-28): the same launch plan as GsaftModel over PcAssocDev
+class PcAssocModel final : public Model {
+public:
+    PcAssocParams p{};
+    int ncomp() const override { return p.pc.nc; }
+    const char* family() const override { return "genericSAFT-PCSAFT"; }
+    double R(const double*, int) const override { return p.pc.R; }
+    const void* params_blob(size_t* n) const override { *n = sizeof(p); return &p; }
+    void launch_ar_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override {
+        generic_check_ar_shape(NT, ND);
+        if (in.npts == 0) return;
+        if (NT == 0) pcassoc_launch_ar_rho(p, ND, in, out, st);
+        else pcassoc_launch_ar_mixed(p, NT, ND, in, out, st);
+    }
+    void launch_virial_table(int NT, int ND, const DeviceBatch& in, double* out, cudaStream_t st) const override { launch_ar_table(NT, ND, in, out, st); }
+    void launch_sigma_derivs(const DeviceBatch& in, const double* v, double* out, cudaStream_t st) const override { pcassoc_launch_sigma(p, in, v, out, st); }
+    void launch_ATrhoXiXj_table(const DeviceBatch& in, int i, int j, double* out, cudaStream_t st) const override { pcassoc_launch_cross2(p, in, i, j, -1, out, st); }
+    void launch_ATrhoXiXjXk_table(const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override { pcassoc_launch_cross3(p, in, i, j, k, out, st); }
+    void launch_ATrhoXi_table(const DeviceBatch& in, double* out, cudaStream_t st) const override {
+        pcassoc_launch_ATrhoXi_part0(p, in, out, st);
+        pcassoc_launch_ATrhoXi_part1(p, in, out, st);
+        pcassoc_launch_ATrhoXi_part2(p, in, out, st);
+    }
+    void launch_isochoric(const DeviceBatch& in, const IsochoricOut& o, cudaStream_t st) const override { pcassoc_launch_isochoric(p, in, o, st); }
+    void launch_isoprops(const DeviceBatch& in, const IsoPropsOut& o, cudaStream_t st) const override {
+        if (in.npts == 0) return;
+        const int nc = p.pc.nc;
+        double *Ls = nullptr, *H = nullptr;
+        TQ_CUDA(cudaMallocAsync(&Ls, sizeof(double) * 6 * (size_t)in.npts, st));
+        pcassoc_launch_ip_part0(p, in, o, Ls, nullptr, st);
+        const bool vec = o.dpdT || o.d2PsirdTdrhoi || o.dpdrhovec || o.pmv || o.chempotVLE || o.dchempotdT || o.dlnphi_dT || o.dlnphi_drho || o.dlnphi_dv;
+        if (vec) pcassoc_launch_ip_part1(p, in, o, Ls, nullptr, st);
+        if (o.dlnphi_dx) {
+            TQ_CUDA(cudaMallocAsync(&H, sizeof(double) * (size_t)nc * nc * (size_t)in.npts, st));
+            IsochoricOut io; io.hess = H;
+            pcassoc_launch_isochoric(p, in, io, st);
+            pcassoc_launch_ip_part2(p, in, o, Ls, H, st);
             TQ_CUDA(cudaFreeAsync(H, st));
         }
         TQ_CUDA(cudaFreeAsync(Ls, st));
@@ -196,6 +255,10 @@ void fill_assoc(AssocParams& a, const Json& j, size_t N) {
         const Json& o = j.at("options");
         a.alpha = o.value("alpha", a.alpha); a.rtol = o.value("rtol", a.rtol); a.atol = o.value("atol", a.atol);
         a.max_iters = (int)o.value("max_iters", (double)a.max_iters);
+        // association_types.hpp:20-28: "CS" (Carnahan-Starling, the default) or "KG"; the device term evaluates CS only
+        const std::string rd = o.value("radial_dist", std::string("CS"));
+        if (rd == "KG") throw NotImplementedError("association option radial_dist = KG is not implemented on the device path (CS is)");
+        if (rd != "CS") throw InvalidArgument("bad radial_dist flag:" + rd);
         if (o.contains("self_association_mask")) {
             const Json& sm = o.at("self_association_mask");
             for (size_t i = 0; i < sm.size(); ++i) self_mask.push_back(sm[i].as_bool());
@@ -313,12 +376,26 @@ std::unique_ptr<Model> make_saftvrmie_model(const Json& spec) {
 }
 
 std::unique_ptr<Model> make_genericsaft_model(const Json& spec) {
-    auto mdl = std::make_unique<GsaftModel>();
-    mdl->fam = "genericSAFT";
     const Json& np = spec.at("nonpolar");
     const std::string kind = np.at("kind").as_string();
+    if (kind == "PCSAFT" || kind == "PC-SAFT") {
+        auto pm = std::make_unique<PcAssocModel>();
+        fill_pcsaft(pm->p.pc, np.at("model"));
+        if (pm->p.pc.nc > kAssocMaxC) throw InvalidArgument("genericSAFT supports at most " + std::to_string(kAssocMaxC) + " components on the device path");
+        pm->p.has_assoc = 0;
+        if (spec.contains("association")) {
+            const Json& as = spec.at("association");
+            const std::string ak = as.at("kind").as_string();
+            if (ak != "canonical" && ak != "Dufal") throw InvalidArgument("Not valid association kind:" + ak);
+            fill_assoc(pm->p.assoc, as.at("model"), (size_t)pm->p.pc.nc);
+            pm->p.has_assoc = 1;
+        }
+        return pm;
+    }
+    auto mdl = std::make_unique<GsaftModel>();
+    mdl->fam = "genericSAFT";
     if (kind == "SAFTVRMie" || kind == "SAFT-VR-Mie") fill_mie(mdl->p.mie, np.at("model"));
-    else if (kind == "PCSAFT" || kind == "PC-SAFT" || kind == "Johnson+Johnson" || kind == "softSAFT" || kind == "2CLJF" || kind == "2CLJ")
+    else if (kind == "Johnson+Johnson" || kind == "softSAFT" || kind == "2CLJF" || kind == "2CLJ")
         throw NotImplementedError("genericSAFT nonpolar kind " + kind + " is not implemented on the device path (SAFT-VR-Mie is)");
     else throw InvalidArgument("Not valid nonpolar kind:" + kind);
     mdl->p.has_assoc = 0;

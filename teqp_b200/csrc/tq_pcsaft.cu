@@ -74,9 +74,8 @@ public:
 
 }  // namespace
 
-std::unique_ptr<Model> make_pcsaft_model(const Json& spec) {
-    auto mdl = std::make_unique<PcsaftModel>();
-    PcsaftParams& p = mdl->p;
+// PCSAFTfactory (pcsaft.hpp:455-513) into the parameter block; also used by genericSAFT with a PC-SAFT non-polar term (tq_gsaft.cu)
+void fill_pcsaft(PcsaftParams& p, const Json& spec) {
     const double (*a)[7] = GS2001_a;
     const double (*b)[7] = GS2001_b;
     if (spec.contains("ab")) {
@@ -125,6 +124,11 @@ std::unique_ptr<Model> make_pcsaft_model(const Json& spec) {
             for (size_t j = 0; j < N; ++j) p.kmat[i * N + j] = jk[i][j].as_double();
         }
     }
+}
+
+std::unique_ptr<Model> make_pcsaft_model(const Json& spec) {
+    auto mdl = std::make_unique<PcsaftModel>();
+    fill_pcsaft(mdl->p, spec);
     return mdl;
 }
 

@@ -20,6 +20,7 @@
 #include "../../teqp_b200/csrc/tq_pcsaft.cuh"
 #include "../../teqp_b200/csrc/tq_assoc.cuh"
 #include "../../teqp_b200/csrc/tq_ideal.cuh"
+#include "../../teqp_b200/csrc/tq_pcassoc.cuh"
 #include "../../teqp_b200/csrc/tq_vle.cuh"
 
 using namespace tq;
@@ -225,6 +226,11 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             generic_table<GsaftDev>(p, p.mie.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
         }
+        if (fam == "genericSAFT-PCSAFT") {
+            const PcAssocParams& p = *static_cast<const PcAssocParams*>(blob);
+            generic_table<PcAssocDev>(p, p.pc.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
         if (fam == "idealgas") {
             const IdealParams& p = *static_cast<const IdealParams*>(blob);
             generic_table<IdealDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
@@ -251,6 +257,7 @@ int emul_extras(const char* json, int what, int NT, int ND, long long npts, cons
         if (fam == "PCSAFT") TQ_FAM(PcsaftDev, PcsaftParams, p.nc)
         if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") TQ_FAM(GsaftDev, GsaftParams, p.mie.nc)
         if (fam == "idealgas" && what == 1) TQ_FAM(IdealDev, IdealParams, p.nc)
+        if (fam == "genericSAFT-PCSAFT") TQ_FAM(PcAssocDev, PcAssocParams, p.pc.nc)
 #undef TQ_FAM
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -296,6 +303,17 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
                 split_ATrhoXi_point<GsaftDev, GsaftDev::kMaxC, 0, 2>(p, ncomp, T[k], rho[k], xx, out + k, npts);
             }
         }
+        else if (fam == "genericSAFT-PCSAFT") {
+            // the three small-jet parts the product launches for this family (PcAssocModel::launch_ATrhoXi_table)
+            const PcAssocParams& p = *static_cast<const PcAssocParams*>(blob);
+            for (long long k = 0; k < npts; ++k) {
+                double xx[PcAssocDev::kMaxC];
+                for (int i = 0; i < ncomp; ++i) xx[i] = x[(long long)i * npts + k];
+                split_ATrhoXi_point<PcAssocDev, PcAssocDev::kMaxC, 1, 1>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+                split_ATrhoXi_point<PcAssocDev, PcAssocDev::kMaxC, 2, 0>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+                split_ATrhoXi_point<PcAssocDev, PcAssocDev::kMaxC, 0, 2>(p, ncomp, T[k], rho[k], xx, out + k, npts);
+            }
+        }
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -314,6 +332,7 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "PCSAFT") dir_xx<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") dir_xx<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "genericSAFT-PCSAFT") dir_xx<PcAssocDev>(*static_cast<const PcAssocParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else throw InvalidArgument("family not wired in the emulation harness: " + fam);
         return 0;
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
@@ -346,6 +365,19 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
                 if (o.dlnphi_dx) generic_ip_X_point<GsaftDev, GsaftDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), H.data(), k, npts);
             }
         }
+        else if (fam == "genericSAFT-PCSAFT") {
+            // the three single-shape parts the product launches for this family (PcAssocModel::launch_isoprops)
+            const PcAssocParams& p = *static_cast<const PcAssocParams*>(blob);
+            std::vector<double> Ls((size_t)6 * npts), H;
+            if (o.dlnphi_dx) { H.resize((size_t)ncomp * ncomp * npts); IsochoricOut io; io.hess = H.data(); generic_iso<PcAssocDev>(p, ncomp, npts, T, rhovec, io); }
+            for (long long k = 0; k < npts; ++k) {
+                double r[PcAssocDev::kMaxC];
+                for (int i = 0; i < ncomp; ++i) r[i] = rhovec[(long long)i * npts + k];
+                generic_ip_L_point<PcAssocDev, PcAssocDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), k, npts);
+                generic_ip_C_point<PcAssocDev, PcAssocDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), k, npts);
+                if (o.dlnphi_dx) generic_ip_X_point<PcAssocDev, PcAssocDev::kMaxC>(p, ncomp, T[k], r, o, Ls.data(), H.data(), k, npts);
+            }
+        }
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
             // same dispatch as GergModel::launch_isoprops
@@ -370,6 +402,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         else if (fam == "idealgas") generic_iso<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "genericSAFT-PCSAFT") generic_iso<PcAssocDev>(*static_cast<const PcAssocParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") {
             const GergProgram& P = *static_cast<const GergProgram*>(blob);
             // same dispatch as GergModel::launch_isochoric: analytic kernel for tau^t shapes and a constant R, jet sweeps otherwise

@@ -147,7 +147,10 @@ class GpuBackend:
 #   pure 4C water       2.0e-11            1.9e-11
 # No second implementation can be closer to the reference than the reference is to the exact value of its own formulas, so these
 # families get ATOL = 2 x (sum of the two columns) as an additional absolute floor (in coefficient space, i.e. times n! m!).
-ATOL_FAMILY = {"MIE1": 1.3e-13, "MIE3": 1.3e-13, "GSAFT_CR1": 3e-13, "GSAFT_C4": 5e-12, "GSAFT_WATER": 8e-11}
+ATOL_FAMILY = {"MIE1": 1.3e-13, "MIE3": 1.3e-13, "GSAFT_CR1": 3e-13, "GSAFT_C4": 5e-12, "GSAFT_WATER": 8e-11,
+               # PC-SAFT non-polar term + the same association code: pure 4C water takes the same closed-form site fraction (association.hpp:403-418),
+               # the binary the damped fixed point
+               "GSAFT_PC_WATER": 8e-11, "GSAFT_PC2": 3e-13}
 ADJ_FACTOR = {"MIE1": 3.0, "MIE3": 3.0, "GSAFT_C4": 3.0, "GSAFT_CR1": 3.0, "GSAFT_WATER": 3.0,
               "MF_CO2_N2": 3.0,      # non-analytic terms: pow chains on jets; 3.2e-14 S against the reference's 1.5e-14 S on Ar24
               "MF_R32_R125": 10.0}   # orders 5 and 6 of get_Ar06n only (density exponents up to 8 through binomials): 1.3e-14 S against the reference's 1.6e-15 S
@@ -347,6 +350,19 @@ def gerg_vs_aga8_golden(be):
     got = be.ar_table(spec, 2, 2, T, rho, x)
     for key, (i, j) in {"ar00": (0, 0), "ar01": (0, 1), "ar02": (0, 2), "ar10": (1, 0), "ar11": (1, 1), "ar20": (2, 0)}.items():
         np.testing.assert_allclose(got[i, j], [p[key] for p in pts], rtol=2e-11, atol=1e-13, err_msg=key)
+
+
+def gsaft_pc_suite(be, oracle, name, n=300):
+    """genericSAFT with a PC-SAFT non-polar term (genericsaft.hpp:20-28, 65-73) through every entry point the SAFT-VR-Mie variant is tested on"""
+    nc = len(cases.SPECS[name][3])
+    ar_tables(be, oracle, name, n=n)
+    isochoric(be, oracle, name, n=n)
+    atrhoxi(be, oracle, name, n=100)
+    sigma_derivs(be, oracle, name, n=100)
+    virials(be, oracle, name, n=100)
+    if nc >= 2:   # (the cross tables need two components; the isoprops checker indexes [Ncomp][npts] arrays)
+        cross_composition(be, oracle, name, n=60)
+        isoprops(be, oracle, name, n=100)
 
 
 def idealgas_suite(be, oracle, name, n=300):

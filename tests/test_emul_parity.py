@@ -114,3 +114,9 @@ def test_idealgas_reference_pins(emul):
 def test_pure_vle(emul, oracle, name):
     """SURVEY 8 row f1: the batched pure-fluid saturation solver against teqp::pure_VLE_T / dpsatdT_pure"""
     assert ps.pure_vle(ps.EmulBackend(emul), oracle, name, n=64) > 0
+
+
+@pytest.mark.parametrize("name", cases.GSAFT_PC_CASES)
+def test_genericsaft_pcsaft(emul, oracle, name):
+    """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""
+    ps.gsaft_pc_suite(ps.EmulBackend(emul), oracle, name, n=300)

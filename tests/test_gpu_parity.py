@@ -340,3 +340,9 @@ def test_point_status(be):
 def test_pure_vle(be, oracle, name):
     """SURVEY 8 row f1: the batched pure-fluid saturation solver against teqp::pure_VLE_T / dpsatdT_pure"""
     assert ps.pure_vle(be, oracle, name, n=2000) > 0
+
+
+@pytest.mark.parametrize("name", cases.GSAFT_PC_CASES)
+def test_genericsaft_pcsaft(be, oracle, name):
+    """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""
+    ps.gsaft_pc_suite(be, oracle, name, n=600)
