@@ -124,6 +124,17 @@ int pure_VLE_T_batch(const long long int uuid, const long long int npts, const d
                      const double* molefrac, const int Ncomp, double* rhoL, double* rhoV, double* psat, double* dpsatdT, const int flags,
                      char* errmsg, int errmsg_length);
 
+/* teqp::mix_VLE_Tx / AbstractModel::mix_VLE_Tx (/root/reference/include/teqp/algorithms/VLE.hpp:76-192) for npts binary-mixture problems at once: T[k]
+   and the liquid mole fraction xspec[0][k] given, unknowns the molar concentrations of both phases; Newton's method on equal chemical potentials,
+   equal pressure and the composition constraint, Jacobian from the Hessians of Psi^r, with the reference's step limiter, frozen zero-mole-fraction
+   components and stopping rules per point.  Every iteration is ONE launch of the isochoric kernel (Psi^r, gradient, Hessian) over the 2 npts liquid +
+   vapour states and one update kernel.  rhovecL0, rhovecV0, xspec, rhovecL, rhovecV: [2][npts].  return_code[k] (optional, doubles) holds
+   teqp::VLE_return_code (VLE_types.hpp:44): 1 xtol_satisfied, 2 functol_satisfied, 4 maxiter_met, 5 notfinite_step, 0 when maxiter = 0.  Two-component
+   models with a composition-independent gas constant only. */
+int mix_VLE_Tx_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovecL0, const double* rhovecV0,
+                     const double* xspec, const double atol, const double reltol, const double axtol, const double relxtol, const int maxiter,
+                     double* rhovecL, double* rhovecV, double* return_code, const int flags, char* errmsg, int errmsg_length);
+
 /* Per-point status of a finished batched call (the "per-point int* status" of SURVEY.md section 8b; the reference throws per call --
    teqp::InvalidArgument / IterationFailure, /root/reference/include/teqp/exceptions.hpp:17-64 -- where a batch can only flag the point):
    status[k] is a bit set computed on the GPU from the inputs of point k and the nrows output rows out[r][k] a previous entry point wrote for it

@@ -397,4 +397,49 @@ int ref_pure_VLE_T(void* h, long long npts, const double* T, const double* rhoL0
         if (dpsatdT) dpsatdT[k] = teqp::dpsatdT_pure(am, T[k], r[0], r[1], zz);
     });
 }
+// teqp::mix_VLE_Tx (algorithms/VLE.hpp:76-192).  ORACLE PORT, not the reference's own function: VLE.hpp cannot be compiled here (it includes
+// critical_tracing.hpp -> boost::numeric::odeint and the multicomplex library, both missing blobs), and the reference holds no stored numbers for this
+// solver ("parity unpinned" for the loop itself).  The restatement follows VLE.hpp:84-191 step by step on the reference's OWN AbstractModel
+// (build_Psir_fgradHessian_autodiff, get_R) and Eigen's colPivHouseholderQr; the tests additionally check the equilibrium conditions at the solution.
+int ref_mix_VLE_Tx(void* h, long long npts, const double* T, const double* rvL0, const double* rvV0, const double* xspec, double atol, double reltol,
+                   double axtol, double relxtol, int maxiter, double* rvL, double* rvV, double* code, int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        const int N = 2;
+        Eigen::MatrixXd J(2 * N, 2 * N), r(2 * N, 1), x(2 * N, 1);
+        Eigen::ArrayXd xs(2); xs << xspec[k], xspec[npts + k];
+        x(0) = rvL0[k]; x(1) = rvL0[npts + k]; x(2) = rvV0[k]; x(3) = rvV0[npts + k];
+        const double RT = am.get_R(xs) * T[k];
+        int rc = 0;                                                                                   // VLE_return_code::unset
+        for (int iter = 0; iter < maxiter; ++iter) {
+            const Eigen::ArrayXd rhovecL = x.col(0).array().head(N), rhovecV = x.col(0).array().tail(N);
+            auto [PsirL, gL, HL] = am.build_Psir_fgradHessian_autodiff(T[k], rhovecL);               // VLE.hpp:96-97
+            auto [PsirV, gV, HV] = am.build_Psir_fgradHessian_autodiff(T[k], rhovecV);
+            const double rhoL = rhovecL.sum(), rhoV = rhovecV.sum();
+            const double pL = rhoL * RT - PsirL + (rhovecL * gL).sum(), pV = rhoV * RT - PsirV + (rhovecV * gV).sum();   // :100-101
+            const Eigen::ArrayXd dpL = RT + (HL.matrix() * rhovecL.matrix()).array(), dpV = RT + (HV.matrix() * rhovecV.matrix()).array();
+            const bool nz0 = rhovecL(0) > 0 && rhovecV(0) > 0, nz1 = rhovecL(1) > 0 && rhovecV(1) > 0;                  // :105-106
+            r(0) = nz0 ? gL(0) + RT * log(rhovecL(0)) - (gV(0) + RT * log(rhovecV(0))) : gL(0) - gV(0);
+            r(1) = nz1 ? gL(1) + RT * log(rhovecL(1)) - (gV(1) + RT * log(rhovecV(1))) : gL(1) - gV(1);
+            r(2) = pL - pV;
+            r(3) = rhovecL(0) / rhovecL.sum() - xs(0);
+            J.setZero();
+            J(0, 0) = HL(0, 0) + (nz0 ? RT / rhovecL(0) : 0); J(0, 1) = HL(0, 1); J(1, 0) = HL(1, 0); J(1, 1) = HL(1, 1) + (nz1 ? RT / rhovecL(1) : 0);
+            J(0, 2) = -(HV(0, 0) + (nz0 ? RT / rhovecV(0) : 0)); J(0, 3) = -HV(0, 1); J(1, 2) = -HV(1, 0); J(1, 3) = -(HV(1, 1) + (nz1 ? RT / rhovecV(1) : 0));
+            J(2, 0) = dpL(0); J(2, 1) = dpL(1); J(2, 2) = -dpV(0); J(2, 3) = -dpV(1);
+            J(3, 0) = (rhoL - rhovecL(0)) / (rhoL * rhoL); J(3, 1) = -rhovecL(0) / (rhoL * rhoL);
+            Eigen::ArrayXd dx = J.colPivHouseholderQr().solve(-r);                                     // :141
+            if ((!dx.isFinite()).all()) { rc = 5; break; }
+            if ((x.array() + dx < 0).any()) { Eigen::ArrayXd dxmax = -x.array(); dx *= (dx / dxmax).minCoeff() / 2; }   // :148-156
+            for (int i = 0; i < 2; ++i) if (xs[i] == 0) { dx[i] = 0; dx[i + 2] = 0; }
+            x.array() += dx;
+            if ((dx.abs() < (axtol + relxtol * x.array().abs())).all()) { rc = 1; break; }
+            if ((r.array().abs() < (atol + reltol * r.array().abs())).all()) { rc = 2; break; }
+            if (((x.array() - dx).abs() < std::numeric_limits<double>::min()).all()) { rc = 1; break; }
+            if (iter == maxiter - 1) rc = 4;
+        }
+        rvL[k] = x(0); rvL[npts + k] = x(1); rvV[k] = x(2); rvV[npts + k] = x(3);
+        if (code) code[k] = rc;
+    });
+}
 } // extern "C"

@@ -250,6 +250,19 @@ class Model:
                                       outs[2].ptr if want_extra else null, outs[3].ptr if want_extra else null, C.c_int(flags), err, C.c_int(2000)), err)
         return outs[0].obj, outs[1].obj, (outs[2].obj if want_extra else None), (outs[3].obj if want_extra else None)
 
+    def mix_VLE_Tx_batch(self, T, rhovecL0, rhovecV0, xspec, atol=1e-10, reltol=1e-10, axtol=1e-10, relxtol=1e-10, maxiter=10):
+        """teqp::mix_VLE_Tx (algorithms/VLE.hpp:76-192) for many binary-mixture problems at once; arrays [2][npts]; returns (rhovecL, rhovecV, return_code)"""
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        aT, aL, aV, ax = _Arg(T, dev), _Arg(rhovecL0, dev), _Arg(rhovecV0, dev), _Arg(xspec, dev)
+        oL, oV, oc = _Arg(self._out((2, n), dev, T), dev), _Arg(self._out((2, n), dev, T), dev), _Arg(self._out((n,), dev, T), dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().mix_VLE_Tx_batch(self._uuid, C.c_longlong(n), aT.ptr, aL.ptr, aV.ptr, ax.ptr, C.c_double(atol), C.c_double(reltol), C.c_double(axtol),
+                                      C.c_double(relxtol), C.c_int(maxiter), oL.ptr, oV.ptr, oc.ptr, C.c_int(flags), err, C.c_int(2000)), err)
+        return oL.obj, oV.obj, oc.obj
+
     def point_status_batch(self, T, rho, x, out=None):
         """int32 [npts] bit set per point (teqpb200.h: 1 bad input, 2 non-finite output, 4 mole fractions do not sum to one) for the inputs of a
         batched call and, if given, the [rows][npts] (or [..., npts]) output array it wrote -- the per-point counterpart of the exceptions the

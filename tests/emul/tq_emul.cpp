@@ -426,4 +426,23 @@ int emul_pure_vle_update(long long n, const double* A, double* rho2, double* don
     return 0;
 }
 
+// one Newton update of the batched binary-mixture solver (mix_vle_update_kernel, tq_vle.cuh): f[2n], g[2][2n], H[4][2n], rv2[2][2n], xspec[2][n], code[n]
+int emul_mix_vle_update(long long n, double R, const double* T, const double* xspec, const double* f, const double* g, const double* H, double atol, double reltol,
+                        double axtol, double relxtol, int last_iter, double* rv2, double* code) {
+    const long long n2 = 2 * n;
+    for (long long k = 0; k < n; ++k) {
+        if (code[k] != 0.0) continue;
+        double x[4] = {rv2[k], rv2[n2 + k], rv2[n + k], rv2[n2 + n + k]};
+        const double gL[2] = {g[k], g[n2 + k]}, gV[2] = {g[n + k], g[n2 + n + k]};
+        double HL[4], HV[4];
+        for (int q = 0; q < 4; ++q) { HL[q] = H[(long long)q * n2 + k]; HV[q] = H[(long long)q * n2 + n + k]; }
+        const double xs[2] = {xspec[k], xspec[n + k]};
+        double c = 0.0;
+        mix_vle_newton_point(R * T[k], f[k], gL, HL, f[n + k], gV, HV, xs, atol, reltol, axtol, relxtol, last_iter != 0, x, c);
+        if (c != 5.0) { rv2[k] = x[0]; rv2[n2 + k] = x[1]; rv2[n + k] = x[2]; rv2[n2 + n + k] = x[3]; }
+        code[k] = c;
+    }
+    return 0;
+}
+
 }  // extern "C"

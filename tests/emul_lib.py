@@ -194,3 +194,11 @@ def pure_vle_update(A, rho2, done):
     A = np.ascontiguousarray(A, dtype=np.float64)
     assert A.shape == (3, 2 * n) and rho2.shape == (2 * n,)
     lib().emul_pure_vle_update(C.c_longlong(n), _p(A), _p(rho2), _p(done))
+
+
+def mix_vle_update(R, T, xspec, f, g, H, tols, last_iter, rv2, code):
+    n = code.size
+    f, g, H, xspec, T = (np.ascontiguousarray(a, dtype=np.float64) for a in (f, g, H, xspec, T))
+    assert f.shape == (2 * n,) and g.shape == (2, 2 * n) and H.shape == (4, 2 * n) and rv2.shape == (2, 2 * n) and xspec.shape == (2, n)
+    lib().emul_mix_vle_update(C.c_longlong(n), C.c_double(R), _p(T), _p(xspec), _p(f), _p(g), _p(H), *(C.c_double(t) for t in tols), C.c_int(int(last_iter)),
+                              _p(rv2), _p(code))

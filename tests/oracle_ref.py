@@ -178,6 +178,15 @@ class RefModel:
         self._call(lib().ref_pure_VLE_T, C.c_longlong(n), _p(T), _p(rhoL0), _p(rhoV0), C.c_int(maxiter), _p(z), C.c_int(z.size), _p(rL), _p(rV), _p(ps), _p(dp))
         return rL, rV, ps, dp
 
+    def mix_VLE_Tx(self, T, rvL0, rvV0, xspec, atol=1e-10, reltol=1e-10, axtol=1e-10, relxtol=1e-10, maxiter=10):
+        """oracle port of teqp::mix_VLE_Tx (VLE.hpp:76-192) on the reference's AbstractModel: (rhovecL [2][n], rhovecV [2][n], return_code [n])"""
+        T = np.ascontiguousarray(T, dtype=np.float64); n = T.size
+        a, b, x = _soa(rvL0, n), _soa(rvV0, n), _soa(xspec, n)
+        oL, oV, oc = np.empty((2, n)), np.empty((2, n)), np.empty(n)
+        self._call(lib().ref_mix_VLE_Tx, C.c_longlong(n), _p(T), _p(a), _p(b), _p(x), C.c_double(atol), C.c_double(reltol), C.c_double(axtol),
+                   C.c_double(relxtol), C.c_int(maxiter), _p(oL), _p(oV), _p(oc))
+        return oL, oV, oc
+
     def deriv_mat2(self, T, rho, x):
         T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
         n = T.size; x = _soa(x, n)

@@ -63,6 +63,16 @@ class EmulBackend:
         dpsatdT = (R * ((B[0, 1, n:] + B[1, 0, n:]) - (B[0, 1, :n] + B[1, 0, :n]))) / (1 / rV - 1 / rL)
         return rL, rV, psat, dpsatdT
 
+    def mix_VLE_Tx(self, spec, T, rvL0, rvV0, xspec, tols, maxiter):
+        """host replay of mix_VLE_Tx_batch (tq_capi.cu): the per-point Newton update of tq_vle.cuh around the replayed isochoric kernel"""
+        n = T.size
+        T2 = np.concatenate([T, T]); rv2 = np.ascontiguousarray(np.concatenate([rvL0, rvV0], axis=1)); code = np.zeros(n)
+        R = float(self._R(spec, [0.25, 0.75]))
+        for it in range(maxiter):
+            f, g, H, _, _ = self.e.isochoric(spec, T2, rv2)
+            self.e.mix_vle_update(R, T, xspec, f, g, H.reshape(4, 2 * n), tols, it == maxiter - 1, rv2, code)
+        return rv2[:, :n].copy(), rv2[:, n:].copy(), code
+
     def _R(self, spec, z):
         import teqp_b200
         import ctypes as C
@@ -123,6 +133,9 @@ class GpuBackend:
 
     def sigma_derivs(self, spec, T, rv, v):
         return self.model(spec).get_Psir_sigma_derivs_batch(T, rv, v)
+
+    def mix_VLE_Tx(self, spec, T, rvL0, rvV0, xspec, tols, maxiter):
+        return self.model(spec).mix_VLE_Tx_batch(T, rvL0, rvV0, xspec, *tols, maxiter=maxiter)
 
     def pure_VLE_T(self, spec, T, rhoL0, rhoV0, maxiter, z):
         return self.model(spec).pure_VLE_T_batch(T, rhoL0, rhoV0, maxiter, np.asarray(z, dtype=np.float64))
@@ -607,3 +620,64 @@ def pure_vle(be, oracle, name, n=64, maxiter=10):
     gibbsL = AL[0] + AL[1] + np.log(gL); gibbsV = AV[0] + AV[1] + np.log(gV)
     assert np.max(np.abs(pL - pV)[ok] / pV[ok]) < 1e-9 and np.max(np.abs(gibbsL - gibbsV)[ok]) < 1e-11
     return int(ok.sum())
+
+
+def pr_mixture_guess(T, x0, Tc, pc, w, kij):
+    """starting values for a binary T-x flash: Wilson K-values and Raoult's law for p and the vapour composition, then the liquid / vapour roots of the
+    Peng-Robinson cubic of the mixture.  Returns rhovecL0, rhovecV0 as [2][n]."""
+    R = 8.31446261815324
+    Tc, pc, w = (np.asarray(a, dtype=np.float64) for a in (Tc, pc, w))
+    n = T.size
+    rvL = np.empty((2, n)); rvV = np.empty((2, n))
+    mm = 0.37464 + 1.54226 * w - 0.26992 * w**2
+    b = 0.077796073903888455972 * R * Tc / pc
+    for k in range(n):
+        x = np.array([x0[k], 1 - x0[k]])
+        ps = pc * np.exp(5.373 * (1 + w) * (1 - Tc / T[k]))
+        p = float(np.sum(x * ps)); y = x * ps / p
+        a = 0.45723552892138218938 * R**2 * Tc**2 / pc * (1 + mm * (1 - np.sqrt(T[k] / Tc)))**2
+        for comp, dst, pick in ((x, rvL, 0), (y, rvV, -1)):
+            am = sum(comp[i] * comp[j] * np.sqrt(a[i] * a[j]) * (1 - (kij if i != j else 0.0)) for i in range(2) for j in range(2))
+            bm = float(np.sum(comp * b))
+            A = am * p / (R * T[k])**2; B = bm * p / (R * T[k])
+            Z = np.roots([1, -(1 - B), A - 3 * B * B - 2 * B, -(A * B - B * B - B**3)])
+            Z = np.sort(Z[np.abs(Z.imag) < 1e-9].real); Z = Z[Z > B]
+            dst[:, k] = comp * p / (Z[pick] * R * T[k])
+    return rvL, rvV
+
+
+# binary T-x flashes: methane (0) + ethane (1); (Tc, pc, acentric, k_ij for the starting guess)
+MIXVLE_CASES = {"PR2k": 0.05, "PCSAFT2": 0.0, "MF_CH4_C2H6_CODATA": 0.0}
+
+
+def mix_vle(be, oracle, name, n=48, maxiter=10):
+    """SURVEY row f1: batched teqp::mix_VLE_Tx (algorithms/VLE.hpp:76-192).  Checker: the oracle's port of that routine on the reference's own
+    AbstractModel (the header itself does not compile here, oracle/ref_capi.cpp) from the same starting values, tolerances and iteration count --
+    same return code per point, concentrations to 1e-9 where it converged -- and, independently of any solver, the equilibrium conditions at the
+    returned state evaluated with the reference: equal pressure (1e-9 relative) and equal chemical potentials (1e-9 RT)."""
+    spec = cases.SPECS[name][0]
+    rng = np.random.RandomState(7)
+    T = 150.0 + 30.0 * rng.rand(n); x0 = 0.05 + 0.4 * rng.rand(n)
+    rvL0, rvV0 = pr_mixture_guess(T, x0, [190.564, 305.322], [4599200.0, 4872200.0], [0.011, 0.099], MIXVLE_CASES[name])
+    xspec = np.ascontiguousarray(np.stack([x0, 1 - x0]))
+    tols = (1e-10, 1e-10, 1e-10, 1e-10)
+    m = oracle.RefModel(spec)
+    rL, rV, rc = m.mix_VLE_Tx(T, rvL0, rvV0, xspec, *tols, maxiter=maxiter)
+    conv = ((rc == 1) | (rc == 2)) & (rL.sum(axis=0) > 1.2 * rV.sum(axis=0))
+    assert conv.mean() > 0.8, "starting values too poor: the reference algorithm converged on %.0f %% of the points" % (100 * conv.mean())
+    gL, gV, gc = be.mix_VLE_Tx(spec, T, rvL0, rvV0, xspec, tols, maxiter)
+    # the last Newton step of a converged point is at rounding level, so which of the two tolerance tests fires first can differ: compare "converged"
+    gconv = (gc == 1) | (gc == 2)
+    assert np.array_equal(gconv[conv], np.ones(int(conv.sum()), bool)), (gc[conv], rc[conv])
+    np.testing.assert_allclose(gL[:, conv], rL[:, conv], rtol=1e-9)
+    np.testing.assert_allclose(gV[:, conv], rV[:, conv], rtol=1e-9)
+    # equilibrium conditions with the reference's own derivatives
+    R = m.get_R(np.array([0.5, 0.5]))
+    fL, grL, _ = m.fgradHessian(T, np.ascontiguousarray(gL)); fV, grV, _ = m.fgradHessian(T, np.ascontiguousarray(gV))
+    RT = R * T
+    pL = gL.sum(axis=0) * RT - fL + (gL * grL).sum(axis=0); pV = gV.sum(axis=0) * RT - fV + (gV * grV).sum(axis=0)
+    muL = grL + RT * np.log(gL); muV = grV + RT * np.log(gV)
+    assert np.max(np.abs(pL / pV - 1)[conv]) < 1e-9
+    assert np.max((np.abs(muL - muV) / RT)[:, conv]) < 1e-9
+    assert np.max(np.abs(gL[0] / gL.sum(axis=0) - x0)[conv]) < 1e-10
+    return int(conv.sum())

@@ -120,3 +120,9 @@ def test_pure_vle(emul, oracle, name):
 def test_genericsaft_pcsaft(emul, oracle, name):
     """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""
     ps.gsaft_pc_suite(ps.EmulBackend(emul), oracle, name, n=300)
+
+
+@pytest.mark.parametrize("name", sorted(ps.MIXVLE_CASES))
+def test_mix_vle_Tx(emul, oracle, name):
+    """the batched binary T-x flash against teqp::mix_VLE_Tx (oracle port) and the equilibrium conditions themselves"""
+    assert ps.mix_vle(ps.EmulBackend(emul), oracle, name, n=48) > 0

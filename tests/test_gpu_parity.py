@@ -346,3 +346,9 @@ def test_pure_vle(be, oracle, name):
 def test_genericsaft_pcsaft(be, oracle, name):
     """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""
     ps.gsaft_pc_suite(be, oracle, name, n=600)
+
+
+@pytest.mark.parametrize("name", sorted(ps.MIXVLE_CASES))
+def test_mix_vle_Tx(be, oracle, name):
+    """the batched binary T-x flash against teqp::mix_VLE_Tx (oracle port) and the equilibrium conditions themselves"""
+    assert ps.mix_vle(be, oracle, name, n=512) > 0
