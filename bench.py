@@ -150,8 +150,11 @@ def make_steps(w, model, nc, n, xp):
         which = ["dlnphi_dT", "dlnphi_drho", "dlnphi_dx"]
 
         def step(I, O):
-            model.build_Psir_fgradHessian_batch(I["T"], I["rv"], out=O[:3])
-            model.isochoric_properties_batch(I["T"], I["rv"], which=which, out=dict(zip(which, O[3:])))
+            if os.environ.get("TEQPB200_C5X_TWO_CALLS"):   # A/B: the two separate entry points
+                model.build_Psir_fgradHessian_batch(I["T"], I["rv"], out=O[:3])
+                model.isochoric_properties_batch(I["T"], I["rv"], which=which, out=dict(zip(which, O[3:])))
+            else:                                          # one call, one launch for the GERG models
+                model.fgradHessian_and_properties_batch(I["T"], I["rv"], which=which, out=O[:3], out_props=dict(zip(which, O[3:])))
         return (lambda mk: (mk((1, n)), mk((nc, n)), mk((nc * nc, n)), mk((nc, n)), mk((nc, n)), mk((nc * nc, n)))), step, 1 + 3 * nc + 2 * nc * nc
     raise SystemExit("unknown workload kind " + what)
 
@@ -501,6 +504,33 @@ def run_ours(args):
                     torch.cuda.empty_cache()
                 except Exception as e:  # a secondary line must never take the headline down
                     sec.append({"config": name, "error": str(e)[:300]})
+            # the batched pure-fluid saturation solver (teqp::pure_VLE_T, 10 Newton iterations per isotherm) on the C1 model
+            try:
+                from teqp_b200.workloads import pr_saturation_guess
+                nv = 10**6
+                Tg = np.linspace(105.0, 185.0, 2048)
+                rLg, rVg = pr_saturation_guess(Tg, 190.564, 4599200.0, 0.011)
+                Tv = np.linspace(105.0, 185.0, nv)
+                dTv = torch.from_numpy(Tv).cuda(); dLv = torch.from_numpy(np.interp(Tv, Tg, rLg)).cuda(); dVv = torch.from_numpy(np.exp(np.interp(Tv, Tg, np.log(rVg)))).cuda()
+                dzv = torch.ones(1, dtype=torch.float64, device="cuda")
+                mv = teqp_b200.make_model(WORKLOADS["C1"]["spec"])
+                l0 = teqp_b200.lib().teqpb200_kernel_launches()
+                for _ in range(3):
+                    ov = mv.pure_VLE_T_batch(dTv, dLv, dVv, 10, dzv)
+                torch.cuda.synchronize()
+                lv = (teqp_b200.lib().teqpb200_kernel_launches() - l0) // 3
+                ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ev0.record()
+                for _ in range(3):
+                    ov = mv.pure_VLE_T_batch(dTv, dLv, dVv, 10, dzv)
+                ev1.record(); torch.cuda.synchronize()
+                msv = ev0.elapsed_time(ev1) / 3
+                okv = bool(torch.isfinite(ov[0]).all() and (ov[0] > 1.2 * ov[1]).all())
+                sec.append({"config": "V1: PR methane, pure_VLE_T_batch (teqp::pure_VLE_T + dpsatdT_pure, 10 Newton iterations) over %d isotherms 105..185 K" % nv,
+                            "value": nv / msv * 1e3, "unit": "isotherms/s", "ms_per_step": msv, "gpu_launches": int(lv), "all_converged_two_phase": okv,
+                            "checksum": float(ov[2].sum().item())})
+            except Exception as e:
+                sec.append({"config": "V1", "error": str(e)[:300]})
             line["secondary"] = sec
         emit(line)
     if dist is not None:

@@ -93,6 +93,13 @@ int isochoric_properties_batch(const long long int uuid, const long long int npt
                                double* pr, double* splus, double* dpdT, double* d2PsirdTdrhoi, double* dpdrhovec, double* pmv,
                                double* chempotVLE, double* dchempotdT, double* dlnphi_dT, double* dlnphi_drho, double* dlnphi_dv,
                                double* dlnphi_dx, const int flags, char* errmsg, int errmsg_length);
+/* build_Psir_fgradHessian_batch AND isochoric_properties_batch in one call (BASELINE config C5: "isochoric Hessian / fugacity composition derivatives"):
+   the same outputs, bit for bit; for the GERG / multifluid term-program models ONE launch of the lane-cooperative kernel produces both (the passes over
+   the reducing pairs and the term program are shared), other families run their two launches inside the call.  Every output may be NULL. */
+int build_Psir_fgradHessian_and_properties_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const int Ncomp,
+                                                 double* f, double* g, double* H, double* pr, double* splus, double* dpdT, double* d2PsirdTdrhoi,
+                                                 double* dpdrhovec, double* pmv, double* chempotVLE, double* dchempotdT, double* dlnphi_dT, double* dlnphi_drho,
+                                                 double* dlnphi_dv, double* dlnphi_dx, const int flags, char* errmsg, int errmsg_length);
 /* IsochoricDerivatives::get_ln_fugacity_coefficients / get_fugacity_coefficients (derivs.hpp:1208-1230): out[i][k] */
 int get_ln_fugacity_coefficients_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec,
                                        const int Ncomp, double* out, const int flags, char* errmsg, int errmsg_length);

@@ -26,6 +26,7 @@ int sm_count() {
     return n;
 }
 
+bool gerg_try_launch_fused(const Model&, const DeviceBatch&, const IsochoricOut&, const IsoPropsOut&, cudaStream_t);   // tq_gerg.cu
 // ideal-gas kinds (tq_ideal.cu)
 std::unique_ptr<Model> make_ideal_helmholtz_model(const Json& jpures);
 std::unique_ptr<Model> make_gerg_idealgas_model(const std::string& kind, const Json& spec);
@@ -726,6 +727,36 @@ int get_Psir_sigma_derivs_batch(const long long int uuid, const long long int np
             [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
                 m->launch_sigma_derivs(make_batch(n, din[0], nullptr, din[1], false), din[2], dout[0], st);
                 ++g_launches;
+            });
+    });
+}
+
+int build_Psir_fgradHessian_and_properties_batch(const long long int uuid, const long long int npts, const double* T, const double* rhovec, const int Ncomp,
+                                                 double* f, double* g, double* H, double* pr, double* splus, double* dpdT, double* d2PsirdTdrhoi,
+                                                 double* dpdrhovec, double* pmv, double* chempotVLE, double* dchempotdT, double* dlnphi_dT, double* dlnphi_drho,
+                                                 double* dlnphi_dv, double* dlnphi_dx, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        check_ncomp(*m, Ncomp);
+        if (flags & TEQPB200_BROADCAST_X) throw InvalidArgument("TEQPB200_BROADCAST_X does not apply to rhovec inputs");
+        double* ptr[15] = {f, g, H, pr, splus, dpdT, d2PsirdTdrhoi, dpdrhovec, pmv, chempotVLE, dchempotdT, dlnphi_dT, dlnphi_drho, dlnphi_dv, dlnphi_dx};
+        const int rows[15] = {1, Ncomp, Ncomp * Ncomp, 1, 1, 1, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp, Ncomp * Ncomp};
+        std::vector<HostOut> outs;
+        int slot[15];
+        for (int q = 0; q < 15; ++q) { slot[q] = -1; if (ptr[q]) { slot[q] = (int)outs.size(); outs.push_back({ptr[q], rows[q]}); } }
+        if (outs.empty()) return;
+        run(flags, npts, {{T, 1, false}, {rhovec, Ncomp, false}}, outs,
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                IsochoricOut io;
+                IsoPropsOut o;
+                double** fld[15] = {&io.Psir, &io.grad, &io.hess, &o.pr, &o.splus, &o.dpdT, &o.d2PsirdTdrhoi, &o.dpdrhovec, &o.pmv, &o.chempotVLE, &o.dchempotdT,
+                                    &o.dlnphi_dT, &o.dlnphi_drho, &o.dlnphi_dv, &o.dlnphi_dx};
+                bool any_iso = false, any_ip = false;
+                for (int q = 0; q < 15; ++q) if (slot[q] >= 0) { *fld[q] = dout[slot[q]]; (q < 3 ? any_iso : any_ip) = true; }
+                const DeviceBatch b = make_batch(n, din[0], nullptr, din[1], false);
+                if (any_iso && any_ip && gerg_try_launch_fused(*m, b, io, o, st)) { ++g_launches; return; }
+                if (any_iso) { m->launch_isochoric(b, io, st); ++g_launches; }
+                if (any_ip) { m->launch_isoprops(b, o, st); ++g_launches; }
             });
     });
 }

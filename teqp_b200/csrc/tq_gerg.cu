@@ -157,6 +157,13 @@ public:
         }
         else gergjet_launch_isochoric(P, in, o, st);
     }
+    // Psir / gradient / Hessian AND the derived properties in one launch of the lane-cooperative kernel (false: not applicable, launch separately)
+    bool launch_fused(const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip, cudaStream_t st) const {
+        static const bool jets = std::getenv("TEQPB200_GERG_ISOPROPS_JETS") != nullptr;
+        if (jets || !src.all_plain_tau || src.has_nonanalytic || P.r_weighted || P.pure_shortcut || !coop_pays()) return false;
+        if (o.lnphi || o.phi) return false;   // the Hessian instantiation serves Psir, grad, hess
+        return gerg_coop_launch_fused(iso_tab, P, Rgas, in, o, ip, st);
+    }
     void launch_Ataudelta_table(int which, const DeviceBatch& in, int i, int j, int k, double* out, cudaStream_t st) const override {
         if (!taudelta_ok()) throw NotImplementedError("Cannot take derivatives of a class that doesn't define the alphar_taudelta method");
         gergtd_launch(P, which, in, i, j, k, out, st);
@@ -398,6 +405,12 @@ std::unique_ptr<Model> make_term_program_model(const TermProgramInput& in) {
 
 namespace {
 }  // namespace
+
+// tq_capi.cu (build_Psir_fgradHessian_and_properties_batch): true when the model is a GERG / multifluid term-program model and the fused launch ran
+bool gerg_try_launch_fused(const Model& m, const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip, cudaStream_t st) {
+    const GergModel* gm = dynamic_cast<const GergModel*>(&m);
+    return gm && gm->launch_fused(in, o, ip, st);
+}
 
 std::unique_ptr<Model> make_gerg_model(const std::string& kind, const Json& spec) {
     const std::vector<std::string> names = spec.at("names").as_strings();

@@ -170,6 +170,12 @@ bool gerg_coop_launch_isoprops(const GergIsoDeviceTables& tab, const GergProgram
     return coop_launch<true, true>(tab, P, Rgas, in, none, ip, st);
 }
 
+bool gerg_coop_launch_fused(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip,
+                            cudaStream_t st) {
+    if (in.npts == 0) return true;
+    return coop_launch<true, true>(tab, P, Rgas, in, o, ip, st);
+}
+
 void gerg_launch_isoprops(const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& ip, cudaStream_t st) {
     if (in.npts == 0) return;
     const size_t rows = (size_t)gerg_iso_rows(P.nc, P.nw, true);

@@ -493,6 +493,9 @@ private:
 // host launchers (tq_gerg_iso.cu); false: the mixture's tables and staging rows do not fit one SM's shared memory (caller falls back)
 bool gerg_coop_launch_isochoric(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o,
                                 cudaStream_t st);
+// both families of outputs from ONE launch (fused C5x step: Psir, gradient, Hessian and the derived properties share passes A, B and C)
+bool gerg_coop_launch_fused(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip,
+                            cudaStream_t st);
 bool gerg_coop_launch_isoprops(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsoPropsOut& o,
                                cudaStream_t st);
 

@@ -161,6 +161,26 @@ class Model:
         _check(lib().isochoric_properties_batch(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *ptrs, C.c_int(flags), err, C.c_int(2000)), err)
         return {k: (outs[k].obj[0] if rows[k] == 1 else outs[k].obj) for k in which}
 
+    def fgradHessian_and_properties_batch(self, T, rhovec, which=None, out=None, out_props=None):
+        """build_Psir_fgradHessian_batch and isochoric_properties_batch in one call (one kernel launch for the GERG / multifluid models):
+        returns (Psir[npts], grad[Ncomp][npts], H[Ncomp][Ncomp][npts], {name: array}); out = (f[1][npts], g, H[Ncomp*Ncomp][npts]) and out_props reuse buffers"""
+        which = list(self.ISOPROPS) if which is None else list(which)
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        nc = rhovec.shape[0]
+        aT, av = _Arg(T, dev), _Arg(rhovec, dev)
+        fgh = [_Arg(self._out((r, n), dev, T, None if out is None else out[q]), dev) for q, r in enumerate([1, nc, nc * nc])]
+        rows = dict(zip(self.ISOPROPS, [1, 1, 1] + [nc] * 8 + [nc * nc]))
+        outs = {k: _Arg(self._out((rows[k], n), dev, T, None if out_props is None else out_props.get(k)), dev) for k in which}
+        null = C.POINTER(C.c_double)()
+        ptrs = [a.ptr for a in fgh] + [outs[k].ptr if k in outs else null for k in self.ISOPROPS]
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().build_Psir_fgradHessian_and_properties_batch(self._uuid, C.c_longlong(n), aT.ptr, av.ptr, C.c_int(nc), *ptrs, C.c_int(flags), err, C.c_int(2000)), err)
+        H = fgh[2].obj
+        return fgh[0].obj[0], fgh[1].obj, H.reshape((nc, nc) + tuple(H.shape[1:])), {k: (outs[k].obj[0] if rows[k] == 1 else outs[k].obj) for k in which}
+
     def build_Psir_fgradHessian_batch(self, T, rhovec, out=None):
         """returns (Psir[npts], grad[Ncomp][npts], H[Ncomp][Ncomp][npts]); out = (f[1][npts], g[Ncomp][npts], H[Ncomp*Ncomp][npts]) reuses buffers"""
         nc = rhovec.shape[0]

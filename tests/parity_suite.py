@@ -568,22 +568,7 @@ def ataudelta(be, oracle, name, n=100):
             parity.check("%s AtaudeltaXi NT%d ND%d X%d^%d" % (name, NT, ND, i, NX), got[i, NT, ND, NX], ref[i, NT, ND, NX], S, ftol=2 * ftol_for(name, ND) * 2**NX)
 
 
-def pr_saturation_guess(T, Tc, pc, acentric):
-    """rough saturation densities for starting values: Wilson's vapour pressure, then the liquid and vapour roots of the Peng-Robinson cubic"""
-    R = 8.31446261815324
-    T = np.asarray(T, dtype=np.float64)
-    p = pc * np.exp(5.373 * (1 + acentric) * (1 - Tc / T))
-    mm = 0.37464 + 1.54226 * acentric - 0.26992 * acentric**2
-    a = 0.45723552892138218938 * R**2 * Tc**2 / pc * (1 + mm * (1 - np.sqrt(T / Tc)))**2
-    b = 0.077796073903888455972 * R * Tc / pc
-    rL = np.empty_like(T); rV = np.empty_like(T)
-    for k in range(T.size):
-        A = a[k] * p[k] / (R * T[k])**2; B = b * p[k] / (R * T[k])
-        Z = np.roots([1, -(1 - B), A - 3 * B * B - 2 * B, -(A * B - B * B - B**3)])
-        Z = np.sort(Z[np.abs(Z.imag) < 1e-9].real)
-        Z = Z[Z > B]
-        rL[k] = p[k] / (Z[0] * R * T[k]); rV[k] = p[k] / (Z[-1] * R * T[k])
-    return rL, rV
+from teqp_b200.workloads import pr_saturation_guess  # noqa: E402  (starting values shared with bench.py's VLE line)
 
 
 # pure-fluid saturation cases: (spec name in cases.SPECS, composition, Tc, pc, acentric for the starting guess, temperature range)

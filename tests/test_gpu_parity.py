@@ -352,3 +352,25 @@ def test_genericsaft_pcsaft(be, oracle, name):
 def test_mix_vle_Tx(be, oracle, name):
     """SURVEY 8 row f1: the batched binary T-x flash against teqp::mix_VLE_Tx (oracle port) and the equilibrium conditions themselves"""
     assert ps.mix_vle(be, oracle, name, n=512) > 0
+
+
+@pytest.mark.parametrize("name", ["GERG21", "GERG10", "PR2k", "PCSAFT2"])
+def test_fused_fgradHessian_and_properties(be, name):
+    """build_Psir_fgradHessian_and_properties_batch == build_Psir_fgradHessian_batch + isochoric_properties_batch, bit for bit (one launch for the GERG kinds)"""
+    import teqp_b200
+    spec, T, rho, x = cases.points(name, 3001)
+    rv = np.ascontiguousarray(x * rho)
+    m = be.model(spec)
+    f0, g0, H0 = m.build_Psir_fgradHessian_batch(T, rv)
+    p0 = m.isochoric_properties_batch(T, rv)
+    l0 = teqp_b200.lib().teqpb200_kernel_launches()
+    f1, g1, H1, p1 = m.fgradHessian_and_properties_batch(T, rv)
+    nl = teqp_b200.lib().teqpb200_kernel_launches() - l0
+    assert np.array_equal(f0, f1) and np.array_equal(g0, g1) and np.array_equal(H0, H1)
+    for k in p0:
+        assert np.array_equal(p0[k], p1[k], equal_nan=True), k
+    if name.startswith("GERG"):
+        assert nl == 1, nl
+    # a subset of the outputs
+    f2, g2, H2, p2 = m.fgradHessian_and_properties_batch(T, rv, which=["dlnphi_dx"])
+    assert np.array_equal(H0, H2) and np.array_equal(p0["dlnphi_dx"], p2["dlnphi_dx"])
