@@ -93,16 +93,16 @@ __global__ void __launch_bounds__(32 * kCoopMaxWarps) gerg_iso_coop_kernel(const
     const int warp = threadIdx.x >> 5, l32 = threadIdx.x & 31;
     const int grp = l32 / L, lane = l32 % L;
     const int wpc = blockDim.x >> 5;
-    double* W = sm + blob_words + (size_t)warp * rows * PPW + grp;
+    double* W = sm + blob_words + (size_t)(warp * PPW + grp) * rows;   // rows = the point stride (gerg_coop_pstride)
     const int nc = reinterpret_cast<const GergIsoHdr*>(sm)->nc;
     const long long stride = (long long)gridDim.x * wpc * PPW;
     for (long long base = ((long long)blockIdx.x * wpc + warp) * PPW; base < in.npts; base += stride) {
         const long long k0 = base + grp;
         const bool valid = k0 < in.npts;
         const long long k = valid ? k0 : in.npts - 1;
-        for (int i = lane; i < nc; i += L) W[i * PPW] = __ldg(in.x + (long long)i * in.x_stride + k);
+        for (int i = lane; i < nc; i += L) W[i] = __ldg(in.x + (long long)i * in.x_stride + k);
         __syncwarp();
-        gerg_iso_coop_point<L, WANT_H>(sm, Rgas, __ldg(in.T + k), W, PPW, lane, valid, o, k, in.npts, IP ? &ip : nullptr);
+        gerg_iso_coop_point<L, WANT_H>(sm, Rgas, __ldg(in.T + k), W, lane, valid, o, k, in.npts, IP ? &ip : nullptr);
         __syncwarp();
     }
 }
@@ -111,7 +111,7 @@ template<int L, bool WANT_H, bool IP>
 bool coop_launch_l(const double* blob_d, const GergIsoHdr& h, double Rgas, const DeviceBatch& in, const IsochoricOut& o, const IsoPropsOut& ip,
                    cudaStream_t st) {
     constexpr int PPW = 32 / L;
-    const int rows = gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, WANT_H);
+    const int rows = gerg_coop_pstride(gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, WANT_H), L);
     const size_t blob_bytes = (size_t)h.nwords * 8, per_warp = (size_t)rows * PPW * 8;
     if (blob_bytes + 2 * per_warp + 1024 > kSmemPerSM) return false;
     int nwarps = (int)std::min<size_t>(kCoopMaxWarps, (kSmemPerSM - 1024 - blob_bytes) / per_warp);
@@ -129,11 +129,15 @@ bool coop_launch_l(const double* blob_d, const GergIsoHdr& h, double Rgas, const
 template<bool WANT_H, bool IP>
 bool coop_launch(const GergIsoDeviceTables& tab, const GergProgram& P, double Rgas, const DeviceBatch& in, const IsochoricOut& o,
                  const IsoPropsOut& ip, cudaStream_t st) {
-    static const int L = [] { const char* e = std::getenv("TEQPB200_ISO_COOP_L"); return e ? std::atoi(e) : 8; }();
+    static const int L = [] {
+        const char* e = std::getenv("TEQPB200_ISO_COOP_L");
+        const int v = e ? std::atoi(e) : 8;
+        return (v == 0 || v == 4 || v == 16) ? v : 8;
+    }();
     if (L == 0) return false;   // TEQPB200_ISO_COOP_L=0: the thread-per-point kernels (A/B measurements)
     int dev = 0;
     TQ_CUDA(cudaGetDevice(&dev));
-    const double* blob_d = tab.on_device(P, dev);
+    const double* blob_d = tab.on_device(P, dev, L);
     const GergIsoHdr& h = *reinterpret_cast<const GergIsoHdr*>(tab.host.data());
     if (L == 4) return coop_launch_l<4, WANT_H, IP>(blob_d, h, Rgas, in, o, ip, st);
     if (L == 16) return coop_launch_l<16, WANT_H, IP>(blob_d, h, Rgas, in, o, ip, st);
@@ -142,9 +146,10 @@ bool coop_launch(const GergIsoDeviceTables& tab, const GergProgram& P, double Rg
 
 }  // namespace
 
-const double* GergIsoDeviceTables::on_device(const GergProgram& P, int dev) const {
+const double* GergIsoDeviceTables::on_device(const GergProgram& P, int dev, int L) const {
     std::lock_guard<std::mutex> g(mtx_);
-    if (host.empty()) const_cast<std::vector<double>&>(host) = gerg_iso_build_blob(P);
+    if (host.empty()) const_cast<std::vector<double>&>(host) = gerg_iso_build_blob(P, L);
+    if (reinterpret_cast<const GergIsoHdr*>(host.data())->L != L) throw InvalidArgument("lane-cooperative tables were built for another number of lanes per point");
     auto it = dev_.find(dev);
     if (it != dev_.end()) return it->second;
     double* d = nullptr;

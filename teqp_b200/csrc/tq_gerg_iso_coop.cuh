@@ -35,16 +35,26 @@ static_assert(sizeof(GergIsoPair) == 32 && sizeof(GergIsoGroup) == 88 && sizeof(
 
 struct GergIsoHdr {   // offsets in 8-byte words from the start of the blob
     int nc, nw, ndep, ngroup, nT, nterm, nwords, pad_;
-    int oTc, ovc, opair, opartner, ongen, orowperm, odepF, odepi, odepj, odepq, oadjs, oadjq, oadjo, otval, ogroup, owperm, owstart, oterm;
+    int oTc, ovc, opair, opartner, ongen, orowperm, odepF, odepi, odepj, odepq, oadjs, oadjq, oadjo, otval, ogroup, owperm;
+    int L, nround, oround, otn, ott, otid;   // term table: lane-interleaved planes for L lanes per point (see gerg_iso_build_blob)
 };
 static_assert(sizeof(GergIsoHdr) % 8 == 0, "header is whole words");
+struct GergIsoRound { int base, len; };   // entries [base + j L + lane], j < len
 
 TQ_HD constexpr int gerg_coop_rows(int nc, int nw, int nT, int ngroup, bool want_h) {
     return want_h ? 4 * nw + 4 * nc + (nc > nT + 3 * ngroup ? nc : nT + 3 * ngroup) : 2 * nw + 2 * nc + nT + 2 * ngroup;
 }
 
+// distance between the staging areas of two points of a warp: the row count rounded up to L (mod 16) doubles, so that the groups that share a
+// shared-memory wavefront (a half-warp for 8-byte accesses: 16 / L groups) sit on disjoint banks when they run the same row pattern
+TQ_HD constexpr int gerg_coop_pstride(int rows, int L) {
+    int p = rows;
+    while ((p & 15) != (L & 15)) ++p;
+    return p;
+}
+
 // ---- host: GergProgram -> blob ---------------------------------------------------------------------------------------------------
-inline std::vector<double> gerg_iso_build_blob(const GergProgram& P) {
+inline std::vector<double> gerg_iso_build_blob(const GergProgram& P, const int L = 1) {
     const int nc = P.nc, nw = P.nw, ndep = P.ndep;
     struct T3 { int w; double n, t; int g; };
     std::vector<T3> terms;
@@ -90,28 +100,48 @@ inline std::vector<double> gerg_iso_build_blob(const GergProgram& P) {
     auto take = [&](size_t bytes) { const int o = words; words += (int)((bytes + 7) / 8); return o; };
     h.oTc = take(8 * nc); h.ovc = take(8 * nc);
     words += words & 1;   // 16-byte alignment of the pair records
-    h.opair = take(sizeof(GergIsoPair) * nc * nc);
+    h.opair = take(sizeof(GergIsoPair) * nc * nc);   // four planes kT, YT, kV, YV of nc*nc doubles (structure of arrays: see pair_at)
     h.opartner = take(partner.size()); h.ongen = take(nc); h.orowperm = take(nc);
     h.odepF = take(8 * std::max(ndep, 1)); h.odepi = take(std::max(ndep, 1)); h.odepj = take(std::max(ndep, 1));
     h.odepq = take((size_t)nc * nc);
     h.oadjs = take(nc + 1); h.oadjq = take(std::max(2 * ndep, 1)); h.oadjo = take(std::max(2 * ndep, 1));
     h.otval = take(8 * nT);
     h.ogroup = take(sizeof(GergIsoGroup) * P.ngroup);
-    h.owperm = take(nw); h.owstart = take(2 * (nw + 1));
-    h.oterm = take(sizeof(GergIsoTerm) * terms.size());
+    h.owperm = take(nw);
+    // Term table.  Lane l of a point walks the weights wperm[l + L m], m = 0, 1, ...: the terms of the L weights of round m are stored interleaved,
+    // entry (j, l) at base_m + j L + l, as three planes (n, t, packed indices), the shorter lists padded with n = 0 entries up to the round's longest
+    // (the weights are sorted by term count, so little is padded).  The lanes of a group then read CONSECUTIVE shared-memory words in every step
+    // (no bank conflicts, no per-lane loop bounds); the 24-byte records of the first version put them on arbitrary banks.
+    h.L = L;
+    h.nround = (nw + L - 1) / L;
+    std::vector<GergIsoRound> rounds((size_t)h.nround);
+    int nent = 0;
+    for (int m = 0; m < h.nround; ++m) {
+        int len = 0;
+        for (int l = 0; l < L && m * L + l < nw; ++l) len = std::max(len, cnt[wperm[m * L + l]]);
+        rounds[m] = {nent, len};
+        nent += len * L;
+    }
+    h.oround = take(sizeof(GergIsoRound) * h.nround);
+    h.otn = take(8 * (size_t)std::max(nent, 1)); h.ott = take(8 * (size_t)std::max(nent, 1)); h.otid = take(4 * (size_t)std::max(nent, 1));
     words += words & 1;
     h.nwords = words;
     std::vector<double> blob((size_t)words, 0.0);
     std::memcpy(blob.data(), &h, sizeof(h));
     auto B = [&](int off) { return reinterpret_cast<unsigned char*>(blob.data() + off); };
     for (int i = 0; i < nc; ++i) { blob[h.oTc + i] = P.Tc[i]; blob[h.ovc + i] = P.vc[i]; }
-    GergIsoPair* pr = reinterpret_cast<GergIsoPair*>(blob.data() + h.opair);
+    // planes instead of records: in pass C the lanes of a group read pairs (a, a + s) for consecutive rows a, i.e. plane indices that differ by
+    // nc + 1 -- distinct shared-memory banks for the usual odd / even nc -- where 32-byte records put every lane on one of four bank groups
     for (int a = 0; a < nc; ++a)
         for (int b = 0; b < nc; ++b) {
-            if (a == b) { pr[a * nc + b] = {1.0, 0.0, 1.0, 0.0}; continue; }
-            const GergRedPair& p = P.pair[a < b ? pidx(a, b) : pidx(b, a)];
-            pr[a * nc + b] = (a < b) ? GergIsoPair{p.beta2T, p.YT2, p.beta2V, p.YV2}
-                                     : GergIsoPair{1.0 / p.beta2T, p.YT2 / p.beta2T, 1.0 / p.beta2V, p.YV2 / p.beta2V};
+            GergIsoPair v{1.0, 0.0, 1.0, 0.0};
+            if (a != b) {
+                const GergRedPair& p = P.pair[a < b ? pidx(a, b) : pidx(b, a)];
+                v = (a < b) ? GergIsoPair{p.beta2T, p.YT2, p.beta2V, p.YV2}
+                            : GergIsoPair{1.0 / p.beta2T, p.YT2 / p.beta2T, 1.0 / p.beta2V, p.YV2 / p.beta2V};
+            }
+            const int q = a * nc + b, n2 = nc * nc;
+            blob[h.opair + q] = v.kT; blob[h.opair + n2 + q] = v.YT; blob[h.opair + 2 * n2 + q] = v.kV; blob[h.opair + 3 * n2 + q] = v.YV;
         }
     std::memcpy(B(h.opartner), partner.data(), partner.size());
     for (int a = 0; a < nc; ++a) { B(h.ongen)[a] = (unsigned char)ngen[a]; B(h.orowperm)[a] = (unsigned char)rowperm[a]; }
@@ -138,16 +168,19 @@ inline std::vector<double> gerg_iso_build_blob(const GergProgram& P) {
         const GergGroup& s = P.group[g];
         gg[g] = {s.kind, s.d, s.l, 0, s.c, s.eta, s.eps, s.beta, s.gamma, s.bd[0], s.bd[1], s.bl[0], s.bl[1]};
     }
-    GergIsoTerm* tt = reinterpret_cast<GergIsoTerm*>(blob.data() + h.oterm);
-    unsigned short* ws = reinterpret_cast<unsigned short*>(blob.data() + h.owstart);
-    int it = 0;
+    std::memcpy(blob.data() + h.oround, rounds.data(), sizeof(GergIsoRound) * rounds.size());
+    int* tid = reinterpret_cast<int*>(blob.data() + h.otid);
     for (int p = 0; p < nw; ++p) {
         B(h.owperm)[p] = (unsigned char)wperm[p];
-        ws[p] = (unsigned short)it;
+        const int m = p / L, l = p % L;
+        int j = 0;
         for (auto& t : terms)
-            if (t.w == wperm[p]) tt[it++] = {t.n, t.t, tix[t.t], t.g};
+            if (t.w == wperm[p]) {
+                const int e = rounds[m].base + j * L + l;
+                blob[h.otn + e] = t.n; blob[h.ott + e] = t.t; tid[e] = tix[t.t] | (t.g << 16);
+                ++j;
+            }
     }
-    ws[nw] = (unsigned short)it;
     return blob;
 }
 
@@ -166,16 +199,16 @@ TQ_HD void lane_sync() {
 #endif
 }
 
-// One state point, shared by L lanes (lane = 0 .. L-1).  W: the point's column of the staging area (row r at W[r * RS]); rows [0, nc)
+// One state point, shared by L lanes (lane = 0 .. L-1).  W: the point's staging rows, contiguous (row r at W[r]); rows [0, nc)
 // hold the molar concentrations on entry.  valid = false: a padding point (all stores suppressed; the lanes still take part in the
 // reductions).  On the host: L = 1.
 template<int L, bool WANT_H>
-TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const double T, double* W, const int RS, const int lane, const bool valid,
+TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const double T, double* W, const int lane, const bool valid,
                                const IsochoricOut& o, const long long k, const long long npts, const IsoPropsOut* ipp = nullptr) {
     const GergIsoHdr& h = *reinterpret_cast<const GergIsoHdr*>(blob);
     const int nc = h.nc, nw = h.nw, ndep = h.ndep;
     auto bytes = [&](int off) { return reinterpret_cast<const unsigned char*>(blob + off); };
-#define TQ_ROW(r) W[(size_t)(r) * RS]
+#define TQ_ROW(r) W[r]
     const int rA = nw, rS = 2 * nw, rR = 3 * nw;
     const int rvt = WANT_H ? 4 * nw : 2 * nw, rvd = rvt + nc;
     const int rDT = rvd + nc, rDV = rDT + nc;
@@ -184,7 +217,9 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
     constexpr int NG = WANT_H ? 3 : 2;
     const double* Tc = blob + h.oTc;
     const double* vc = blob + h.ovc;
-    const GergIsoPair* pair = reinterpret_cast<const GergIsoPair*>(blob + h.opair);
+    const double* pairp = blob + h.opair;
+    const int n2 = nc * nc;
+    auto pair_at = [&](int q) { return GergIsoPair{pairp[q], pairp[n2 + q], pairp[2 * n2 + q], pairp[3 * n2 + q]}; };
 
     // ---- pass A ------------------------------------------------------------------------------------------------------------------
     double rsum = 0.0, YT1 = 0.0, YV1 = 0.0, YT2 = 0.0, YV2 = 0.0;
@@ -199,14 +234,14 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
             YT1 = fma(ra * ra, Tc[a], YT1);
             YV1 = fma(ra * ra, vc[a], YV1);
             double gT = 2.0 * ra * Tc[a], gV = 2.0 * ra * vc[a], DT = 0.0, DV = 0.0;
-            const GergIsoPair* pa = pair + a * nc;
+            const int pa = a * nc;
             const unsigned char* pl = partner + a * (nc - 1);
             const int ng = ngen[a];
             int idx = 0;
             for (; idx < ng; ++idx) {
                 const int b = pl[idx];
                 const double rb = TQ_ROW(b);
-                const GergIsoPair pr = pa[b];
+                const GergIsoPair pr = pair_at(pa + b);
                 const double dT = fma(pr.kT, ra, rb), dV = fma(pr.kV, ra, rb);
                 const double den = dT * dV;
                 if (den == 0.0) continue;   // both concentrations zero: the reference skips the pair (GERG.hpp:189)
@@ -227,12 +262,12 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
             for (; idx < nc - 1; ++idx) {   // beta_T = beta_v = 1: u = ra rb (zero, with zero gradient, when the pair is skipped)
                 const int b = pl[idx];
                 const double rb = TQ_ROW(b);
-                const GergIsoPair pr = pa[b];
+                const double prYT = pairp[n2 + pa + b], prYV = pairp[3 * n2 + pa + b];
                 const double pab = ra * rb;
-                YT2 = fma(pr.YT, pab, YT2);
-                YV2 = fma(pr.YV, pab, YV2);
-                gT = fma(pr.YT, rb, gT);
-                gV = fma(pr.YV, rb, gV);
+                YT2 = fma(prYT, pab, YT2);
+                YV2 = fma(prYV, pab, YV2);
+                gT = fma(prYT, rb, gT);
+                gV = fma(prYV, rb, gV);
             }
             TQ_ROW(rvt + a) = gT;
             TQ_ROW(rvd + a) = gV;
@@ -298,32 +333,40 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
     double A00 = 0.0, A10 = 0.0, A01 = 0.0, A20 = 0.0, A11 = 0.0, A02 = 0.0;
     {
         const unsigned char* wperm = bytes(h.owperm);
-        const unsigned short* wstart = reinterpret_cast<const unsigned short*>(blob + h.owstart);
-        const GergIsoTerm* term = reinterpret_cast<const GergIsoTerm*>(blob + h.oterm);
-        for (int p = lane; p < nw; p += L) {
-            const int w = wperm[p];
+        const GergIsoRound* round = reinterpret_cast<const GergIsoRound*>(blob + h.oround);
+        const double* tn = blob + h.otn;
+        const double* tt = blob + h.ott;
+        const int* tid = reinterpret_cast<const int*>(blob + h.otid);
+        const int nround = h.nround;
+        for (int m = 0, p = lane; m < nround; ++m, p += L) {
             double a = 0.0, s = 0.0, r = 0.0, ss = 0.0, sr = 0.0, rr = 0.0;
-            const int i1 = wstart[p + 1];
-            for (int it = wstart[p]; it < i1; ++it) {
-                const GergIsoTerm tm = term[it];
-                const double x = tm.n * TQ_ROW(rTt + tm.ti);
-                const double y = x * tm.t;
-                const double G0 = TQ_ROW(rGt + NG * tm.gi), G1 = TQ_ROW(rGt + NG * tm.gi + 1);
+            const GergIsoRound rd = round[m];
+            int e = rd.base + lane;
+            for (int j = 0; j < rd.len; ++j, e += L) {   // the same trip count for every lane: padded entries have n = 0
+                const int id = tid[e];
+                const double tmt = tt[e];
+                const int ti = id & 0xffff, gi = NG * (id >> 16);
+                const double x = tn[e] * TQ_ROW(rTt + ti);
+                const double y = x * tmt;
+                const double G0 = TQ_ROW(rGt + gi), G1 = TQ_ROW(rGt + gi + 1);
                 a = fma(x, G0, a);
                 s = fma(y, G0, s);
                 r = fma(x, G1, r);
                 if (WANT_H) {
-                    const double G2 = TQ_ROW(rGt + NG * tm.gi + 2);
-                    ss = fma(y * fma(0.5, tm.t, -0.5), G0, ss);
+                    const double G2 = TQ_ROW(rGt + gi + 2);
+                    ss = fma(y * fma(0.5, tmt, -0.5), G0, ss);
                     sr = fma(y, G1, sr);
                     rr = fma(x, G2, rr);
                 }
             }
-            const double Ww = TQ_ROW(w);
-            TQ_ROW(rA + w) = a;
-            if (WANT_H) { TQ_ROW(rS + w) = s; TQ_ROW(rR + w) = r; }
-            A00 = fma(Ww, a, A00); A10 = fma(Ww, s, A10); A01 = fma(Ww, r, A01);
-            if (WANT_H) { A20 = fma(Ww, ss, A20); A11 = fma(Ww, sr, A11); A02 = fma(Ww, rr, A02); }
+            if (p < nw) {
+                const int w = wperm[p];
+                const double Ww = TQ_ROW(w);
+                TQ_ROW(rA + w) = a;
+                if (WANT_H) { TQ_ROW(rS + w) = s; TQ_ROW(rR + w) = r; }
+                A00 = fma(Ww, a, A00); A10 = fma(Ww, s, A10); A01 = fma(Ww, r, A01);
+                if (WANT_H) { A20 = fma(Ww, ss, A20); A11 = fma(Ww, sr, A11); A02 = fma(Ww, rr, A02); }
+            }
         }
     }
     A00 = lane_sum<L>(A00) + nanfix; A10 = lane_sum<L>(A10) + nanfix; A01 = lane_sum<L>(A01) + nanfix;
@@ -422,13 +465,13 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
             if (ip.dlnphi_dv) ip.dlnphi_dv[oa] = -dr * (rhotot * rhotot);
         }
         const double dZxa = Qa + dZx0;
-        const GergIsoPair* pa = pair + a * nc;
+        const int pa = a * nc;
         const int ns = nstep + (((nc & 1) == 0 && a < nc / 2) ? 1 : 0);   // even nc: the antipodal pair belongs to its lower row
         int b = a;
         for (int s = 1; s <= ns; ++s) {
             b = (b + 1 == nc) ? 0 : b + 1;
             const double rb = TQ_ROW(b);
-            const GergIsoPair pr = pa[b];
+            const GergIsoPair pr = pair_at(pa + b);
             double yT = 0.0, yV = 0.0;   // Y_ab / Y
             if (pr.kT == 1.0 && pr.kV == 1.0) {
                 if (ra + rb != 0.0) { yT = pr.YT * iYT; yV = pr.YV * iYV; }
@@ -483,7 +526,7 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
 class GergIsoDeviceTables {
 public:
     std::vector<double> host;
-    const double* on_device(const GergProgram& P, int dev) const;   // tq_gerg_iso.cu
+    const double* on_device(const GergProgram& P, int dev, int L) const;   // tq_gerg_iso.cu; L: lanes per point the term table is laid out for
     ~GergIsoDeviceTables();
 private:
     mutable std::mutex mtx_;

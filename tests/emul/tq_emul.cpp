@@ -119,8 +119,8 @@ void gerg_iso_loop(const GergProgram& P, double Rgas, long long npts, const doub
         std::vector<double> W((size_t)gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, true));
         for (long long k = 0; k < npts; ++k) {
             for (int i = 0; i < P.nc; ++i) W[(size_t)i] = rv[(long long)i * npts + k];
-            if (o.hess) gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, o, k, npts);
-            else gerg_iso_coop_point<1, false>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, o, k, npts);
+            if (o.hess) gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 0, true, o, k, npts);
+            else gerg_iso_coop_point<1, false>(blob.data(), Rgas, T[k], W.data(), 0, true, o, k, npts);
         }
         return;
     }
@@ -141,7 +141,7 @@ void gerg_ip_loop(const GergProgram& P, double Rgas, long long npts, const doubl
         std::vector<double> W((size_t)gerg_coop_rows(h.nc, h.nw, h.nT, h.ngroup, true));
         for (long long k = 0; k < npts; ++k) {
             for (int i = 0; i < P.nc; ++i) W[(size_t)i] = rv[(long long)i * npts + k];
-            gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 1, 0, true, none, k, npts, &ip);
+            gerg_iso_coop_point<1, true>(blob.data(), Rgas, T[k], W.data(), 0, true, none, k, npts, &ip);
         }
         return;
     }

@@ -354,10 +354,31 @@ def test_mix_vle_Tx(be, oracle, name):
     assert ps.mix_vle(be, oracle, name, n=512) > 0
 
 
+class _FusedBackend:
+    """routes the isochoric / isoprops checks of the parity suite through build_Psir_fgradHessian_and_properties_batch"""
+    name = "gpu-fused"
+
+    def __init__(self, be):
+        self.be = be
+
+    def isochoric(self, spec, T, rv):
+        m = self.be.model(spec)
+        f, g, H, _ = m.fgradHessian_and_properties_batch(T, rv, which=["dlnphi_dx"])
+        return f, g, H, m.get_ln_fugacity_coefficients_batch(T, rv), m.get_fugacity_coefficients_batch(T, rv)
+
+    def isoprops(self, spec, T, rv):
+        return self.be.model(spec).fgradHessian_and_properties_batch(T, rv)[3]
+
+
 @pytest.mark.parametrize("name", ["GERG21", "GERG10", "PR2k", "PCSAFT2"])
-def test_fused_fgradHessian_and_properties(be, name):
-    """build_Psir_fgradHessian_and_properties_batch == build_Psir_fgradHessian_batch + isochoric_properties_batch, bit for bit (one launch for the GERG kinds)"""
+def test_fused_fgradHessian_and_properties(be, oracle, name):
+    """build_Psir_fgradHessian_and_properties_batch: parity with the oracle on every output (the isochoric and isoprops checks of the suite), one launch
+    for the GERG kinds, and agreement with the two separate entry points (bit for bit except the Hessian of the GERG kinds, where the two kernel
+    instantiations contract a few multiply-adds differently: a few ulp of the row scale)"""
     import teqp_b200
+    fb = _FusedBackend(be)
+    ps.isochoric(fb, oracle, name, n=(200 if name == "GERG21" else 600), lnphi=False)
+    ps.isoprops(fb, oracle, name, n=(60 if name == "GERG21" else 300))
     spec, T, rho, x = cases.points(name, 3001)
     rv = np.ascontiguousarray(x * rho)
     m = be.model(spec)
@@ -366,11 +387,14 @@ def test_fused_fgradHessian_and_properties(be, name):
     l0 = teqp_b200.lib().teqpb200_kernel_launches()
     f1, g1, H1, p1 = m.fgradHessian_and_properties_batch(T, rv)
     nl = teqp_b200.lib().teqpb200_kernel_launches() - l0
-    assert np.array_equal(f0, f1) and np.array_equal(g0, g1) and np.array_equal(H0, H1)
+    assert np.array_equal(f0, f1) and np.array_equal(g0, g1)
+    scale = np.max(np.abs(H0), axis=(0, 1))
+    assert np.max(np.abs(H0 - H1) / scale) < 2e-15, np.max(np.abs(H0 - H1) / scale)
     for k in p0:
         assert np.array_equal(p0[k], p1[k], equal_nan=True), k
     if name.startswith("GERG"):
         assert nl == 1, nl
-    # a subset of the outputs
+    else:
+        assert np.array_equal(H0, H1)
     f2, g2, H2, p2 = m.fgradHessian_and_properties_batch(T, rv, which=["dlnphi_dx"])
-    assert np.array_equal(H0, H2) and np.array_equal(p0["dlnphi_dx"], p2["dlnphi_dx"])
+    assert np.array_equal(H1, H2) and np.array_equal(p0["dlnphi_dx"], p2["dlnphi_dx"])
