@@ -142,6 +142,12 @@ int mix_VLE_Tx_batch(const long long int uuid, const long long int npts, const d
                      const double* xspec, const double atol, const double reltol, const double axtol, const double relxtol, const int maxiter,
                      double* rhovecL, double* rhovecV, double* return_code, const int flags, char* errmsg, int errmsg_length);
 
+/* teqp::mix_VLE_Tp (VLE.hpp:196-380, the Newton branch :351-367) for npts binary problems at once: T[k] and p[k] given, unknowns the molar concentrations of
+   both phases; residuals equal chemical potentials, (p_V - p)/p and (p_L - p)/p; exactly maxiter Newton steps with the reference's step limiter and no stopping
+   rule (the reference has none).  Launch structure and array layouts of mix_VLE_Tx_batch. */
+int mix_VLE_Tp_batch(const long long int uuid, const long long int npts, const double* T, const double* p, const double* rhovecL0, const double* rhovecV0,
+                     const int maxiter, double* rhovecL, double* rhovecV, const int flags, char* errmsg, int errmsg_length);
+
 /* Per-point status of a finished batched call (the "per-point int* status" of SURVEY.md section 8b; the reference throws per call --
    teqp::InvalidArgument / IterationFailure, /root/reference/include/teqp/exceptions.hpp:17-64 -- where a batch can only flag the point):
    status[k] is a bit set computed on the GPU from the inputs of point k and the nrows output rows out[r][k] a previous entry point wrote for it

@@ -442,4 +442,37 @@ int ref_mix_VLE_Tx(void* h, long long npts, const double* T, const double* rvL0,
         if (code) code[k] = rc;
     });
 }
+// teqp::mix_VLE_Tp, Newton branch (algorithms/VLE.hpp:196-272 residuals / Jacobian, :351-367 loop).  ORACLE PORT for the same reason as ref_mix_VLE_Tx.
+int ref_mix_VLE_Tp(void* h, long long npts, const double* T, const double* pg, const double* rvL0, const double* rvV0, int maxiter, double* rvL, double* rvV,
+                   int nthreads, char* err, int errlen) {
+    const AbstractModel& am = *static_cast<RefModel*>(h)->am;
+    return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
+        const int N = 2;
+        Eigen::MatrixXd J(2 * N, 2 * N);
+        Eigen::VectorXd r(2 * N), x(2 * N);
+        x(0) = rvL0[k]; x(1) = rvL0[npts + k]; x(2) = rvV0[k]; x(3) = rvV0[npts + k];
+        const double p = pg[k];
+        for (int iter = 0; iter < maxiter; ++iter) {
+            const Eigen::ArrayXd rhovecL = x.array().head(N), rhovecV = x.array().tail(N);
+            const double RT = am.get_R((rhovecL / rhovecL.sum()).eval()) * T[k];                       // :209
+            auto [PsirL, gL, HL] = am.build_Psir_fgradHessian_autodiff(T[k], rhovecL);
+            auto [PsirV, gV, HV] = am.build_Psir_fgradHessian_autodiff(T[k], rhovecV);
+            const double rhoL = rhovecL.sum(), rhoV = rhovecV.sum();
+            const double pL = rhoL * RT - PsirL + (rhovecL * gL).sum(), pV = rhoV * RT - PsirV + (rhovecV * gV).sum();
+            const Eigen::ArrayXd dpL = RT + (HL.matrix() * rhovecL.matrix()).array(), dpV = RT + (HV.matrix() * rhovecV.matrix()).array();
+            const bool nz0 = rhovecL(0) > 0 && rhovecV(0) > 0, nz1 = rhovecL(1) > 0 && rhovecV(1) > 0;
+            r(0) = nz0 ? gL(0) + RT * log(rhovecL(0)) - (gV(0) + RT * log(rhovecV(0))) : gL(0) - gV(0);
+            r(1) = nz1 ? gL(1) + RT * log(rhovecL(1)) - (gV(1) + RT * log(rhovecV(1))) : gL(1) - gV(1);
+            r(2) = (pV - p) / p; r(3) = (pL - p) / p;                                                  // :231-232
+            J.setZero();
+            J(0, 0) = HL(0, 0) + (nz0 ? RT / rhovecL(0) : 0); J(0, 1) = HL(0, 1); J(1, 0) = HL(1, 0); J(1, 1) = HL(1, 1) + (nz1 ? RT / rhovecL(1) : 0);
+            J(0, 2) = -(HV(0, 0) + (nz0 ? RT / rhovecV(0) : 0)); J(0, 3) = -HV(0, 1); J(1, 2) = -HV(1, 0); J(1, 3) = -(HV(1, 1) + (nz1 ? RT / rhovecV(1) : 0));
+            J(2, 2) = dpV(0) / p; J(2, 3) = dpV(1) / p; J(3, 0) = dpL(0) / p; J(3, 1) = dpL(1) / p;     // :261-270
+            Eigen::ArrayXd dx = J.colPivHouseholderQr().solve(-r);
+            if ((x.array() + dx < 0).any()) { Eigen::ArrayXd dxmax = -x.array(); dx *= (dx / dxmax).minCoeff() / 2; }
+            x.array() += dx;
+        }
+        rvL[k] = x(0); rvL[npts + k] = x(1); rvV[k] = x(2); rvV[npts + k] = x(3);
+    });
+}
 } // extern "C"

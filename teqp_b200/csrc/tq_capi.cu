@@ -844,6 +844,40 @@ int mix_VLE_Tx_batch(const long long int uuid, const long long int npts, const d
     });
 }
 
+int mix_VLE_Tp_batch(const long long int uuid, const long long int npts, const double* T, const double* p, const double* rhovecL0, const double* rhovecV0,
+                     const int maxiter, double* rhovecL, double* rhovecV, const int flags, char* errmsg, int errmsg_length) {
+    return guarded(false, errmsg, errmsg_length, [&] {
+        auto m = lookup(uuid);
+        if (m->ncomp() != 2) throw InvalidArgument("mix_VLE_Tp is for binary mixtures (VLE.hpp:196-272); this model has " + std::to_string(m->ncomp()) + " components");
+        if (maxiter < 0) throw InvalidArgument("maxiter must be non-negative");
+        if (!rhovecL || !rhovecV) throw InvalidArgument("rhovecL and rhovecV must not be null");
+        if (flags & TEQPB200_BROADCAST_X) throw InvalidArgument("TEQPB200_BROADCAST_X does not apply");
+        const double xa[2] = {0.25, 0.75}, xb[2] = {0.75, 0.25};
+        const double R = m->R(xa, 2);
+        if (R != m->R(xb, 2)) throw NotImplementedError("mix_VLE_Tp_batch needs a composition-independent gas constant (this model weights R by mole fractions)");
+        run(flags, npts, {{T, 1, false}, {p, 1, false}, {rhovecL0, 2, false}, {rhovecV0, 2, false}},
+            {{rhovecL, 2}, {rhovecV, 2}, {nullptr, 1}, {nullptr, 2}, {nullptr, 4}, {nullptr, 2}, {nullptr, 4}, {nullptr, 8}},
+            [&](long long n, const std::vector<const double*>& din, const std::vector<double*>& dout, cudaStream_t st) {
+                double *code = dout[2], *T2 = dout[3], *rv2 = dout[4], *f = dout[5], *g = dout[6], *H = dout[7];
+                const int grid = grid_for(n, 256, sm_count() * 8);
+                mix_vle_init_kernel<<<grid, 256, 0, st>>>(n, din[0], din[2], din[3], T2, rv2, code);
+                TQ_CUDA(cudaGetLastError());
+                ++g_launches;
+                const DeviceBatch b2 = make_batch(2 * n, T2, nullptr, rv2, false);
+                IsochoricOut io; io.Psir = f; io.grad = g; io.hess = H;
+                for (int it = 0; it < maxiter; ++it) {
+                    m->launch_isochoric(b2, io, st);
+                    mix_vle_tp_update_kernel<<<grid, 256, 0, st>>>(n, R, din[0], din[1], f, g, H, rv2);
+                    TQ_CUDA(cudaGetLastError());
+                    g_launches += 2;
+                }
+                mix_vle_finish_kernel<<<grid, 256, 0, st>>>(n, rv2, dout[0], dout[1]);
+                TQ_CUDA(cudaGetLastError());
+                ++g_launches;
+            });
+    });
+}
+
 int teqpb200_point_status_batch(const long long int uuid, const long long int npts, const double* T, const double* rho, const double* molefrac,
                                 const int Ncomp, const int nrows, const double* out, int* status, const int flags, char* errmsg, int errmsg_length) {
     return guarded(false, errmsg, errmsg_length, [&] {

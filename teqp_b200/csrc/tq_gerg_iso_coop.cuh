@@ -342,6 +342,7 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
             double a = 0.0, s = 0.0, r = 0.0, ss = 0.0, sr = 0.0, rr = 0.0;
             const GergIsoRound rd = round[m];
             int e = rd.base + lane;
+#pragma unroll 2
             for (int j = 0; j < rd.len; ++j, e += L) {   // the same trip count for every lane: padded entries have n = 0
                 const int id = tid[e];
                 const double tmt = tt[e];
@@ -468,7 +469,8 @@ TQ_HD void gerg_iso_coop_point(const double* blob, const double Rgas, const doub
         const int pa = a * nc;
         const int ns = nstep + (((nc & 1) == 0 && a < nc / 2) ? 1 : 0);   // even nc: the antipodal pair belongs to its lower row
         int b = a;
-        for (int s = 1; s <= ns; ++s) {
+#pragma unroll 2
+        for (int s = 1; s <= ns; ++s) {   // two partners in flight: their dependency chains interleave
             b = (b + 1 == nc) ? 0 : b + 1;
             const double rb = TQ_ROW(b);
             const GergIsoPair pr = pair_at(pa + b);

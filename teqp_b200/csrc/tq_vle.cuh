@@ -153,6 +153,50 @@ TQ_HD bool mix_vle_newton_point(const double RT, const double fL, const double* 
     return false;
 }
 
+// teqp::mix_VLE_Tp (VLE.hpp:196-380): T and p given, unknowns the four molar concentrations; residuals of hybrj_functor__mix_VLE_Tp::operator() (:204-233: equal
+// chemical potentials, (p_V - p)/p, (p_L - p)/p), Jacobian of ::df (:234-272), and the plain Newton loop of :351-367 -- step limiter only, no stopping rule:
+// every point takes maxiter steps, as the reference does.
+TQ_HD void mix_vle_tp_newton_point(const double RT, const double p, const double fL, const double* gL, const double* HL, const double fV, const double* gV,
+                                   const double* HV, double* x /* rhoL0, rhoL1, rhoV0, rhoV1 */) {
+    const double rhoL = x[0] + x[1], rhoV = x[2] + x[3];
+    const double pL = rhoL * RT - fL + (x[0] * gL[0] + x[1] * gL[1]);
+    const double pV = rhoV * RT - fV + (x[2] * gV[0] + x[3] * gV[1]);
+    const double dpL0 = RT + (HL[0] * x[0] + HL[1] * x[1]), dpL1 = RT + (HL[2] * x[0] + HL[3] * x[1]);
+    const double dpV0 = RT + (HV[0] * x[2] + HV[1] * x[3]), dpV1 = RT + (HV[2] * x[2] + HV[3] * x[3]);
+    const bool nz0 = x[0] > 0 && x[2] > 0, nz1 = x[1] > 0 && x[3] > 0;
+    const double r0 = nz0 ? gL[0] + RT * log(x[0]) - (gV[0] + RT * log(x[2])) : gL[0] - gV[0];
+    const double r1 = nz1 ? gL[1] + RT * log(x[1]) - (gV[1] + RT * log(x[3])) : gL[1] - gV[1];
+    const double r2 = (pV - p) / p, r3 = (pL - p) / p;
+    double J[4][5] = {
+        {HL[0] + (nz0 ? RT / x[0] : 0.0), HL[1], -(HV[0] + (nz0 ? RT / x[2] : 0.0)), -HV[1], -r0},
+        {HL[2], HL[3] + (nz1 ? RT / x[1] : 0.0), -HV[2], -(HV[3] + (nz1 ? RT / x[3] : 0.0)), -r1},
+        {0.0, 0.0, dpV0 / p, dpV1 / p, -r2},
+        {dpL0 / p, dpL1 / p, 0.0, 0.0, -r3}};
+    for (int c = 0; c < 4; ++c) {
+        int piv = c;
+        for (int q = c + 1; q < 4; ++q) if (fabs(J[q][c]) > fabs(J[piv][c])) piv = q;
+        if (piv != c) for (int k = 0; k < 5; ++k) { const double t = J[c][k]; J[c][k] = J[piv][k]; J[piv][k] = t; }
+        for (int q = c + 1; q < 4; ++q) {
+            const double m = J[q][c] / J[c][c];
+            for (int k = c; k < 5; ++k) J[q][k] -= m * J[c][k];
+        }
+    }
+    double dx[4];
+    for (int c = 3; c >= 0; --c) {
+        double s = J[c][4];
+        for (int k = c + 1; k < 4; ++k) s -= J[c][k] * dx[k];
+        dx[c] = s / J[c][c];
+    }
+    bool neg = false;
+    for (int c = 0; c < 4; ++c) if (x[c] + dx[c] < 0) neg = true;
+    if (neg) {
+        double fmin = dx[0] / (-x[0]);
+        for (int c = 1; c < 4; ++c) { const double q = dx[c] / (-x[c]); if (q < fmin) fmin = q; }
+        for (int c = 0; c < 4; ++c) dx[c] *= fmin / 2;
+    }
+    for (int c = 0; c < 4; ++c) x[c] += dx[c];
+}
+
 #if defined(__CUDACC__)
 // rv2: [2][2n] molar concentrations of the 2n-point isochoric batch ([0, n) liquid, [n, 2n) vapour)
 __global__ void __launch_bounds__(256) mix_vle_init_kernel(const long long n, const double* __restrict__ T, const double* __restrict__ rvL0,
@@ -183,6 +227,20 @@ __global__ void __launch_bounds__(256) mix_vle_update_kernel(const long long n, 
         mix_vle_newton_point(R * T[k], f[k], gL, HL, f[n + k], gV, HV, xs, atol, reltol, axtol, relxtol, last_iter != 0, x, c);
         if (c != 5.0) { rv2[k] = x[0]; rv2[n2 + k] = x[1]; rv2[n + k] = x[2]; rv2[n2 + n + k] = x[3]; }   // notfinite_step leaves the densities unchanged
         code[k] = c;
+    }
+}
+__global__ void __launch_bounds__(256) mix_vle_tp_update_kernel(const long long n, const double R, const double* __restrict__ T, const double* __restrict__ p,
+                                                                const double* __restrict__ f, const double* __restrict__ g, const double* __restrict__ H,
+                                                                double* __restrict__ rv2) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long n2 = 2 * n;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) {
+        double x[4] = {rv2[k], rv2[n2 + k], rv2[n + k], rv2[n2 + n + k]};
+        const double gL[2] = {g[k], g[n2 + k]}, gV[2] = {g[n + k], g[n2 + n + k]};
+        double HL[4], HV[4];
+        for (int q = 0; q < 4; ++q) { HL[q] = H[(long long)q * n2 + k]; HV[q] = H[(long long)q * n2 + n + k]; }
+        mix_vle_tp_newton_point(R * T[k], p[k], f[k], gL, HL, f[n + k], gV, HV, x);
+        rv2[k] = x[0]; rv2[n2 + k] = x[1]; rv2[n + k] = x[2]; rv2[n2 + n + k] = x[3];
     }
 }
 __global__ void __launch_bounds__(256) mix_vle_finish_kernel(const long long n, const double* __restrict__ rv2, double* __restrict__ rvL, double* __restrict__ rvV) {

@@ -283,6 +283,18 @@ class Model:
                                       C.c_double(relxtol), C.c_int(maxiter), oL.ptr, oV.ptr, oc.ptr, C.c_int(flags), err, C.c_int(2000)), err)
         return oL.obj, oV.obj, oc.obj
 
+    def mix_VLE_Tp_batch(self, T, p, rhovecL0, rhovecV0, maxiter=10):
+        """teqp::mix_VLE_Tp (algorithms/VLE.hpp:196-380) for many binary problems at once; rhovec arrays [2][npts]; returns (rhovecL, rhovecV)"""
+        dev = _is_torch(T)
+        flags = DEVICE_PTRS if dev else 0
+        n = int(T.numel() if dev else np.size(T))
+        aT, ap, aL, aV = _Arg(T, dev), _Arg(p, dev), _Arg(rhovecL0, dev), _Arg(rhovecV0, dev)
+        oL, oV = _Arg(self._out((2, n), dev, T), dev), _Arg(self._out((2, n), dev, T), dev)
+        err = C.create_string_buffer(2000)
+        self._enter(dev)
+        _check(lib().mix_VLE_Tp_batch(self._uuid, C.c_longlong(n), aT.ptr, ap.ptr, aL.ptr, aV.ptr, C.c_int(maxiter), oL.ptr, oV.ptr, C.c_int(flags), err, C.c_int(2000)), err)
+        return oL.obj, oV.obj
+
     def point_status_batch(self, T, rho, x, out=None):
         """int32 [npts] bit set per point (teqpb200.h: 1 bad input, 2 non-finite output, 4 mole fractions do not sum to one) for the inputs of a
         batched call and, if given, the [rows][npts] (or [..., npts]) output array it wrote -- the per-point counterpart of the exceptions the

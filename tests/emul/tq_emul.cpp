@@ -445,4 +445,18 @@ int emul_mix_vle_update(long long n, double R, const double* T, const double* xs
     return 0;
 }
 
+// one Newton update of mix_VLE_Tp_batch (mix_vle_tp_update_kernel, tq_vle.cuh)
+int emul_mix_vle_tp_update(long long n, double R, const double* T, const double* p, const double* f, const double* g, const double* H, double* rv2) {
+    const long long n2 = 2 * n;
+    for (long long k = 0; k < n; ++k) {
+        double x[4] = {rv2[k], rv2[n2 + k], rv2[n + k], rv2[n2 + n + k]};
+        const double gL[2] = {g[k], g[n2 + k]}, gV[2] = {g[n + k], g[n2 + n + k]};
+        double HL[4], HV[4];
+        for (int q = 0; q < 4; ++q) { HL[q] = H[(long long)q * n2 + k]; HV[q] = H[(long long)q * n2 + n + k]; }
+        mix_vle_tp_newton_point(R * T[k], p[k], f[k], gL, HL, f[n + k], gV, HV, x);
+        rv2[k] = x[0]; rv2[n2 + k] = x[1]; rv2[n + k] = x[2]; rv2[n2 + n + k] = x[3];
+    }
+    return 0;
+}
+
 }  // extern "C"

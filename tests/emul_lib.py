@@ -202,3 +202,10 @@ def mix_vle_update(R, T, xspec, f, g, H, tols, last_iter, rv2, code):
     assert f.shape == (2 * n,) and g.shape == (2, 2 * n) and H.shape == (4, 2 * n) and rv2.shape == (2, 2 * n) and xspec.shape == (2, n)
     lib().emul_mix_vle_update(C.c_longlong(n), C.c_double(R), _p(T), _p(xspec), _p(f), _p(g), _p(H), *(C.c_double(t) for t in tols), C.c_int(int(last_iter)),
                               _p(rv2), _p(code))
+
+
+def mix_vle_tp_update(R, T, p, f, g, H, rv2):
+    n = T.size
+    f, g, H, T, p = (np.ascontiguousarray(a, dtype=np.float64) for a in (f, g, H, T, p))
+    assert f.shape == (2 * n,) and g.shape == (2, 2 * n) and H.shape == (4, 2 * n) and rv2.shape == (2, 2 * n)
+    lib().emul_mix_vle_tp_update(C.c_longlong(n), C.c_double(R), _p(T), _p(p), _p(f), _p(g), _p(H), _p(rv2))

@@ -187,6 +187,14 @@ class RefModel:
                    C.c_double(relxtol), C.c_int(maxiter), _p(oL), _p(oV), _p(oc))
         return oL, oV, oc
 
+    def mix_VLE_Tp(self, T, p, rvL0, rvV0, maxiter=10):
+        """oracle port of teqp::mix_VLE_Tp (VLE.hpp:196-380, Newton branch): (rhovecL [2][n], rhovecV [2][n])"""
+        T = np.ascontiguousarray(T, dtype=np.float64); p = np.ascontiguousarray(p, dtype=np.float64); n = T.size
+        a, b = _soa(rvL0, n), _soa(rvV0, n)
+        oL, oV = np.empty((2, n)), np.empty((2, n))
+        self._call(lib().ref_mix_VLE_Tp, C.c_longlong(n), _p(T), _p(p), _p(a), _p(b), C.c_int(maxiter), _p(oL), _p(oV))
+        return oL, oV
+
     def deriv_mat2(self, T, rho, x):
         T = np.ascontiguousarray(T, dtype=np.float64); rho = np.ascontiguousarray(rho, dtype=np.float64)
         n = T.size; x = _soa(x, n)

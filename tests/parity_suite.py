@@ -73,6 +73,15 @@ class EmulBackend:
             self.e.mix_vle_update(R, T, xspec, f, g, H.reshape(4, 2 * n), tols, it == maxiter - 1, rv2, code)
         return rv2[:, :n].copy(), rv2[:, n:].copy(), code
 
+    def mix_VLE_Tp(self, spec, T, p, rvL0, rvV0, maxiter):
+        n = T.size
+        T2 = np.concatenate([T, T]); rv2 = np.ascontiguousarray(np.concatenate([rvL0, rvV0], axis=1))
+        R = float(self._R(spec, [0.25, 0.75]))
+        for _ in range(maxiter):
+            f, g, H, _, _ = self.e.isochoric(spec, T2, rv2)
+            self.e.mix_vle_tp_update(R, T, p, f, g, H.reshape(4, 2 * n), rv2)
+        return rv2[:, :n].copy(), rv2[:, n:].copy()
+
     def _R(self, spec, z):
         import teqp_b200
         import ctypes as C
@@ -133,6 +142,9 @@ class GpuBackend:
 
     def sigma_derivs(self, spec, T, rv, v):
         return self.model(spec).get_Psir_sigma_derivs_batch(T, rv, v)
+
+    def mix_VLE_Tp(self, spec, T, p, rvL0, rvV0, maxiter):
+        return self.model(spec).mix_VLE_Tp_batch(T, p, rvL0, rvV0, maxiter=maxiter)
 
     def mix_VLE_Tx(self, spec, T, rvL0, rvV0, xspec, tols, maxiter):
         return self.model(spec).mix_VLE_Tx_batch(T, rvL0, rvV0, xspec, *tols, maxiter=maxiter)
@@ -666,3 +678,33 @@ def mix_vle(be, oracle, name, n=48, maxiter=10):
     assert np.max((np.abs(muL - muV) / RT)[:, conv]) < 1e-9
     assert np.max(np.abs(gL[0] / gL.sum(axis=0) - x0)[conv]) < 1e-10
     return int(conv.sum())
+
+
+def mix_vle_tp(be, oracle, name, n=48, maxiter=10):
+    """SURVEY row f1: batched teqp::mix_VLE_Tp (algorithms/VLE.hpp:196-380, Newton branch).  The problems are built from converged T-x flashes: their pressure
+    becomes the specification, the starting values are the converged concentrations perturbed by a few per cent.  Checker: the oracle's port on the
+    reference's AbstractModel (1e-9 on the concentrations) and the conditions themselves with the reference's derivatives: p_L = p_V = p (1e-9),
+    equal chemical potentials (1e-9 RT)."""
+    spec = cases.SPECS[name][0]
+    rng = np.random.RandomState(11)
+    T = 150.0 + 30.0 * rng.rand(n); x0 = 0.05 + 0.4 * rng.rand(n)
+    rvL0, rvV0 = pr_mixture_guess(T, x0, [190.564, 305.322], [4599200.0, 4872200.0], [0.011, 0.099], MIXVLE_CASES[name])
+    m = oracle.RefModel(spec)
+    sL, sV, rc = m.mix_VLE_Tx(T, rvL0, rvV0, np.ascontiguousarray(np.stack([x0, 1 - x0])), maxiter=12)
+    ok = ((rc == 1) | (rc == 2)) & (sL.sum(axis=0) > 1.2 * sV.sum(axis=0))
+    assert ok.mean() > 0.8
+    R = m.get_R(np.array([0.5, 0.5])); RT = R * T
+    fV, grV, _ = m.fgradHessian(T, np.ascontiguousarray(sV))
+    p = sV.sum(axis=0) * RT - fV + (sV * grV).sum(axis=0)
+    pert = 1.0 + 0.02 * (2 * rng.rand(2, n) - 1)
+    gL0 = np.ascontiguousarray(sL * pert); gV0 = np.ascontiguousarray(sV * pert[::-1])
+    rL, rV = m.mix_VLE_Tp(T, p, gL0, gV0, maxiter)
+    gL, gV = be.mix_VLE_Tp(spec, T, p, gL0, gV0, maxiter)
+    np.testing.assert_allclose(gL[:, ok], rL[:, ok], rtol=1e-9)
+    np.testing.assert_allclose(gV[:, ok], rV[:, ok], rtol=1e-9)
+    fL, grL, _ = m.fgradHessian(T, np.ascontiguousarray(gL)); fV, grV, _ = m.fgradHessian(T, np.ascontiguousarray(gV))
+    pL = gL.sum(axis=0) * RT - fL + (gL * grL).sum(axis=0); pV = gV.sum(axis=0) * RT - fV + (gV * grV).sum(axis=0)
+    assert np.max(np.abs(pL / p - 1)[ok]) < 1e-9 and np.max(np.abs(pV / p - 1)[ok]) < 1e-9
+    muL = grL + RT * np.log(gL); muV = grV + RT * np.log(gV)
+    assert np.max((np.abs(muL - muV) / RT)[:, ok]) < 1e-9
+    return int(ok.sum())

@@ -126,3 +126,9 @@ def test_genericsaft_pcsaft(emul, oracle, name):
 def test_mix_vle_Tx(emul, oracle, name):
     """SURVEY 8 row f1: the batched binary T-x flash against teqp::mix_VLE_Tx (oracle port) and the equilibrium conditions themselves"""
     assert ps.mix_vle(ps.EmulBackend(emul), oracle, name, n=48) > 0
+
+
+@pytest.mark.parametrize("name", sorted(ps.MIXVLE_CASES))
+def test_mix_vle_Tp(emul, oracle, name):
+    """SURVEY 8 row f1: the batched binary T-p flash against teqp::mix_VLE_Tp (oracle port) and the equilibrium conditions themselves"""
+    assert ps.mix_vle_tp(ps.EmulBackend(emul), oracle, name, n=48) > 0

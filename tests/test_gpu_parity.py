@@ -398,3 +398,9 @@ def test_fused_fgradHessian_and_properties(be, oracle, name):
         assert np.array_equal(H0, H1)
     f2, g2, H2, p2 = m.fgradHessian_and_properties_batch(T, rv, which=["dlnphi_dx"])
     assert np.array_equal(H1, H2) and np.array_equal(p0["dlnphi_dx"], p2["dlnphi_dx"])
+
+
+@pytest.mark.parametrize("name", sorted(ps.MIXVLE_CASES))
+def test_mix_vle_Tp(be, oracle, name):
+    """SURVEY 8 row f1: the batched binary T-p flash against teqp::mix_VLE_Tp (oracle port) and the equilibrium conditions themselves"""
+    assert ps.mix_vle_tp(be, oracle, name, n=512) > 0
