@@ -211,6 +211,17 @@ EMatrixd B200Model::get_ln_fugacity_coefficients_batch(const REArrayd& T, const 
     return out;
 }
 
+EMatrixd B200Model::pure_VLE_T_batch(const REArrayd& T, const REArrayd& rhoL0, const REArrayd& rhoV0, int maxiter, const std::optional<EArrayd>& molefracs) const {
+    const EArrayd Tc = T, L0 = rhoL0, V0 = rhoV0;
+    if (L0.size() != Tc.size() || V0.size() != Tc.size()) throw teqp::InvalidArgument("T, rhoL0 and rhoV0 must have the same length");
+    EArrayd z = molefracs ? molefracs.value() : EArrayd::Ones(1).eval();
+    if (z.size() != ncomp_) throw teqp::InvalidArgument("molefracs must have one entry per component");
+    EMatrixd out(Tc.size(), 4);   // column-major: four contiguous columns
+    TQ_CALL(::pure_VLE_T_batch(uuid_, Tc.size(), Tc.data(), L0.data(), V0.data(), maxiter, z.data(), ncomp_, out.data(), out.data() + Tc.size(), out.data() + 2 * Tc.size(),
+                               out.data() + 3 * Tc.size(), 0, ERRARGS));
+    return out;
+}
+
 std::unique_ptr<teqp::cppinterface::AbstractModel> factory(const nlohmann::json& j) { return std::make_unique<B200Model>(j); }
 
 }  // namespace teqp_b200

@@ -11,6 +11,7 @@
 
 #include "b200_model.hpp"
 #include "teqp/exceptions.hpp"
+#include "teqp/algorithms/VLE_pure.hpp"   // the reference's own teqp::pure_VLE_T / dpsatdT_pure (what AbstractModel::pure_VLE_T forwards to)
 
 std::unique_ptr<teqp::cppinterface::AbstractModel> teqp_ref_oracle_make_model(const nlohmann::json& j);   // oracle/ref_capi.cpp
 
@@ -18,13 +19,13 @@ using teqp::cppinterface::AbstractModel;
 using teqp::cppinterface::ModelPointerFactoryFunction;
 
 namespace {
-// the registry of teqp_impl_factory.cpp:104-147, restated: kind -> factory; make_model looks the kind up and passes spec["model"]
+// the registry of teqp_impl_factory.cpp:104-147, restated: kind -> factory; make_model_local (teqp: make_model) looks the kind up and passes spec["model"]
 std::map<std::string, ModelPointerFactoryFunction> registry;
 void register_factory(const std::string& key, ModelPointerFactoryFunction& func) {
     if (registry.count(key)) throw teqp::InvalidArgument("key is already present, overwriting is not currently allowed");
     registry[key] = func;
 }
-std::unique_ptr<AbstractModel> make_model(const nlohmann::json& j) { return registry.at(j.at("kind"))(j.at("model")); }
+std::unique_ptr<AbstractModel> make_model_local(const nlohmann::json& j) { return registry.at(j.at("kind"))(j.at("model")); }
 
 int failures = 0, checks = 0;
 void close(const char* what, double got, double ref, double scale, double rtol = 1e-12, double ftol = 2e-14) {
@@ -44,7 +45,7 @@ template<class A, class B> void close_arr(const char* what, const A& got, const 
 
 void compare(const char* label, const nlohmann::json& spec, double T, double rho, const Eigen::ArrayXd& z, bool multifluid_like, bool has_isoprops) {
     std::printf("== %s\n", label);
-    const auto gpu = make_model({{"kind", "B200"}, {"model", spec}});
+    const auto gpu = make_model_local({{"kind", "B200"}, {"model", spec}});
     const auto ref = teqp_ref_oracle_make_model(spec);
     const AbstractModel& a = *gpu;
     const AbstractModel& b = *ref;
@@ -137,7 +138,7 @@ int main() {
         compare("SAFT-VR-Mie methane", nlohmann::json::parse(R"({"kind":"SAFT-VR-Mie","model":{"names":["Methane"]}})"), 200.0, 5000.0, z1, false, false);
         // batched extension == the scalar virtual
         {
-            const auto gpu = make_model({{"kind", "B200"}, {"model", nlohmann::json::parse(R"({"kind":"GERG2008resid","model":{"names":["nitrogen","methane","ethane"]}})")}});
+            const auto gpu = make_model_local({{"kind", "B200"}, {"model", nlohmann::json::parse(R"({"kind":"GERG2008resid","model":{"names":["nitrogen","methane","ethane"]}})")}});
             const auto& m = dynamic_cast<const teqp_b200::B200Model&>(*gpu);
             const int n = 1000;
             Eigen::ArrayXd T = Eigen::ArrayXd::LinSpaced(n, 250, 450), rho = Eigen::ArrayXd::LinSpaced(n, 10, 20000);
@@ -148,6 +149,24 @@ int main() {
                 const Eigen::ArrayXd zk = x.row(k).transpose();
                 const auto one = gpu->get_Ar04n(T[k], rho[k], zk);
                 for (int j = 0; j < 5; ++j) { ++checks; if (out(k, j) != one[j]) { ++failures; std::printf("FAIL batch != scalar at %d,%d\n", k, j); } }
+            }
+        }
+        // batched saturation solver == the reference's pure_VLE_T driven by the reference's own adapter, isotherm by isotherm
+        {
+            const auto spec = nlohmann::json::parse(R"({"kind":"PR","model":{"Tcrit / K":[190.564],"pcrit / Pa":[4599200],"acentric":[0.011]}})");
+            const auto gpu = make_model_local({{"kind", "B200"}, {"model", spec}});
+            const auto ref = teqp_ref_oracle_make_model(spec);
+            const auto& m = dynamic_cast<const teqp_b200::B200Model&>(*gpu);
+            Eigen::ArrayXd T(4), rL0(4), rV0(4);
+            T << 120.0, 140.0, 160.0, 180.0;
+            rL0 << 25500.0, 23500.0, 21000.0, 17000.0;     // rough Peng-Robinson saturation densities of methane
+            rV0 << 170.0, 570.0, 1500.0, 3800.0;
+            const auto out = m.pure_VLE_T_batch(T, rL0, rV0, 10);
+            for (int k = 0; k < 4; ++k) {
+                const auto r = teqp::pure_VLE_T(*ref, T[k], rL0[k], rV0[k], 10);
+                const double dp = teqp::dpsatdT_pure(*ref, T[k], r[0], r[1]);
+                ++checks; if (!(std::abs(out(k, 0) / r[0] - 1) < 1e-10 && std::abs(out(k, 1) / r[1] - 1) < 1e-10 && r[0] > 1.2 * r[1])) { ++failures; std::printf("FAIL pure_VLE_T_batch at %g K: %.15g %.15g vs %.15g %.15g\n", T[k], out(k, 0), out(k, 1), r[0], r[1]); }
+                ++checks; if (!(std::abs(out(k, 3) / dp - 1) < 1e-9)) { ++failures; std::printf("FAIL dpsatdT at %g K: %.15g vs %.15g\n", T[k], out(k, 3), dp); }
             }
         }
     } catch (const std::exception& e) { std::printf("EXCEPTION %s\n", e.what()); return 2; }
