@@ -404,3 +404,38 @@ def test_fused_fgradHessian_and_properties(be, oracle, name):
 def test_mix_vle_Tp(be, oracle, name):
     """SURVEY 8 row f1: the batched binary T-p flash against teqp::mix_VLE_Tp (oracle port) and the equilibrium conditions themselves"""
     assert ps.mix_vle_tp(be, oracle, name, n=512) > 0
+
+
+@pytest.mark.parametrize("what", ["atrhoxi", "cross", "sigma", "isoprops_jets", "multifluid", "taudelta"])
+def test_gerg_jet_kernels_first_in_a_fresh_process(what):
+    """regression (r02w): the GERG / multifluid jet-sweep kernels (3.3 KB local frame, 32 KB parameter block) faulted with an illegal memory access
+    when they were the first large-frame kernel of a process -- cudaLimitStackSize was still 1024 and the driver did not grow the local memory for
+    them; every full test run hid it because kernels of other families ran first.  Each call below is the FIRST GPU work of a new process."""
+    import os
+    import subprocess
+    import sys
+    code = r'''
+import sys, os
+sys.path.insert(0, "."); sys.path.insert(0, "tests")
+import numpy as np
+import teqp_b200, cases
+what = sys.argv[1]
+name = "MF_N2" if what == "multifluid" else ("MF_CH4_N2_O2" if what == "taudelta" else "GERG2004_3")
+spec, T, rho, x = cases.points(name, 257)
+m = teqp_b200.make_model(spec)
+rv = np.ascontiguousarray(x * rho)
+if what == "atrhoxi": out = m.get_ATrhoXi_table_batch(T, rho, x)[:, :2, :2, :]
+elif what == "cross": out = m.get_ATrhoXiXj_table_batch(0, 1, T, rho, x)
+elif what == "sigma": out = m.get_Psir_sigma_derivs_batch(T, rv, np.ascontiguousarray(rv * 0.1))
+elif what == "isoprops_jets": out = m.isochoric_properties_batch(T, rv, which=["dlnphi_dx"])["dlnphi_dx"]
+elif what == "multifluid": out = m.get_Ar0n_batch(4, T, rho, x)
+else: out = m.get_AtaudeltaXi_table_batch(np.full(T.size, 1.1), np.full(T.size, 0.7), x)[:, :2, :2, :]
+assert np.all(np.isfinite(out)), "non-finite output"
+print("ok")
+'''
+    env = dict(os.environ)
+    if what == "isoprops_jets":
+        env["TEQPB200_GERG_ISOPROPS_JETS"] = "1"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code, what], cwd=root, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ok" in r.stdout, (r.stdout[-500:], r.stderr[-1500:])
