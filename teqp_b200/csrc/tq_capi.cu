@@ -242,11 +242,32 @@ void run_host(long long npts, const std::vector<HostIn>& ins, const std::vector<
     for (int d = 0; d < nd; ++d) if (codes[d]) throw Error(codes[d], "device " + std::to_string(devs[d]) + ": " + errs[d]);
 }
 
+// Device-pointer calls take their scratch rows from the device's default stream-ordered memory pool (cudaMallocAsync).  With the pool's default release
+// threshold of zero every synchronisation hands the freed blocks back to the driver, and the next call pays for mapping several hundred MB again
+// (measured: 4 - 40 ms per call of pure_VLE_T_batch on 2 10^6 isotherms, against 1.5 ms of kernels).  The library therefore lets the pool keep up to
+// 8 GiB cached between calls (once per device); teqpb200_release_scratch() trims it.
+void scratch_pool_setup() {
+    static std::mutex mtx;
+    static bool done[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+    std::lock_guard<std::mutex> g(mtx);
+    if (done[dev]) return;
+    cudaMemPool_t pool = nullptr;
+    if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess && pool) {
+        unsigned long long thr = 8ull << 30;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    cudaGetLastError();
+    done[dev] = true;
+}
+
 // one entry point for both pointer kinds
 void run(int flags, long long npts, const std::vector<HostIn>& ins, const std::vector<HostOut>& outs, const ChunkFn& fn) {
     if (npts < 0) throw InvalidArgument("npts must be non-negative");
     if (npts == 0) return;
     if (flags & TEQPB200_DEVICE_PTRS) {
+        scratch_pool_setup();
         std::vector<const double*> din; std::vector<double*> dout;
         std::vector<double*> scratch;
         for (auto& a : ins) din.push_back(a.p);
@@ -476,6 +497,7 @@ static void virial_call(const Model& m, int Nvir, int NTd, long long npts, const
     double* zeros_d = nullptr;
     const double* rho = nullptr;
     if (flags & TEQPB200_DEVICE_PTRS) {
+        scratch_pool_setup();
         TQ_CUDA(cudaMallocAsync(&zeros_d, sizeof(double) * (size_t)npts, tl_stream));
         TQ_CUDA(cudaMemsetAsync(zeros_d, 0, sizeof(double) * (size_t)npts, tl_stream));
         rho = zeros_d;
@@ -773,8 +795,12 @@ int pure_VLE_T_batch(const long long int uuid, const long long int npts, const d
         const bool want_extra = psat || dpsatdT;
         double R = 0.0;
         if (want_extra) {   // AbstractModel::get_R(molefrac) on the host (VLE_pure.hpp:163): the composition is one Ncomp-vector
-            std::vector<double> xh((size_t)Ncomp);
-            if (flags & TEQPB200_DEVICE_PTRS) {
+            std::vector<double> xh((size_t)Ncomp, 1.0 / Ncomp), xalt((size_t)Ncomp, 0.0);
+            xalt[0] = 1.0;
+            const bool r_const = m->R(xh.data(), Ncomp) == m->R(xalt.data(), Ncomp);   // every kind but the mole-fraction-weighted multifluid R
+            if (r_const) {
+                // no need to read the composition back from the device (a stream synchronisation per call)
+            } else if (flags & TEQPB200_DEVICE_PTRS) {
                 TQ_CUDA(cudaMemcpyAsync(xh.data(), molefrac, sizeof(double) * Ncomp, cudaMemcpyDeviceToHost, tl_stream));
                 TQ_CUDA(cudaStreamSynchronize(tl_stream));
             } else {
@@ -985,6 +1011,10 @@ int teqpb200_release_scratch(void) {
         }
     }
     cudaSetDevice(cur);
+    {   // and the stream-ordered scratch the device-pointer calls left cached in the default memory pool (scratch_pool_setup)
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, cur) == cudaSuccess && pool) { cudaDeviceSynchronize(); cudaMemPoolTrimTo(pool, 0); }
+    }
     cudaGetLastError();
     return 0;
 }
