@@ -201,6 +201,11 @@ REF_NOISE_S = {"MF_CH4_N2_O2": 3.3e-13, "MF_CH4_C2H6_CODATA": 1.7e-12, "MF_N2": 
 # case, Lambda_20 / Lambda_30 / Lambda_40): the oracle sits 1.0e-14 / 2.6e-14 / 8.9e-14 S from the exact value, the kernels (which evaluate
 # |y| - ln 2 + ln(1 -/+ exp(-2|y|)), tq_ideal.cuh) 7.5e-16 / 7.3e-16 / 8.3e-16 S.
 REF_NOISE_S.update({"IG_GERG2008_5": 9e-14, "IG_GERG2004_3": 9e-14, "IG_GERG2008_21": 9e-14})
+# Quantum-corrected PR: the Twu alpha function of hydrogen (L = 156.21, M N = -0.031) forms L (1 - Tr^(M N)), a 30-fold cancellation, and the
+# double-precision a_i, b_i carry their rounding into every derivative.  Measured against a 60-digit evaluation of the same formulas
+# (tools/adjudicate_qcpr.py, 100 points per case, Lambda_20 / 30 / 40): the oracle sits up to 2.5e-13 / 1.8e-12 / 8.3e-13 S from the exact value
+# (mean 2e-14 .. 5e-14 S), the kernels the same to two digits.
+REF_NOISE_S.update({"QCPR_H2": 2.5e-13, "QCPR_H2NE": 1.8e-12, "QCPR_FUNNY_R": 8.3e-13})
 
 
 def ftol_for(name, density_order=None):
@@ -216,6 +221,15 @@ def extra_scale(name):
 
 def floor_limit(name, order):
     """upper bound on the fraction of points that may need the absolute floor although the value is significant (|ref| >= 1e-2 S)"""
+    if name.startswith("QCPR"):
+        # composition derivatives of the quantum-corrected PR are ill-conditioned in the double-precision covolumes / attraction parameters: measured
+        # against a 60-digit mpmath evaluation of the same formulas (100 points of QCPR_FUNNY_R, X_i^2 / X_i^3 of get_ATrhoXi) the ORACLE sits
+        # 3.2e-14 .. 1.6e-13 S (mean) and up to 5.7e-12 S (max) from the exact value, the kernels the same to three digits, while kernel and oracle
+        # differ from each other by at most 9.7e-14 S -- so a few points per hundred exceed 1e-12 |ref| at values of 0.01 .. 0.1 S.  Temperature
+        # derivatives: hydrogen's Twu exponent L (1 - Tr^(M N)) with L = 156.21 carries an absolute rounding error of L eps = 1.7e-14, i.e. a relative
+        # error of 1.7e-14 in a(T) in EITHER implementation (the measured mean distance of the oracle from the exact Lambda_40 is 2e-14 S): every
+        # Lambda_n0 below about 0.02 S then differs by more than 1e-12 |ref| (28 % of the points of the pure-hydrogen case)
+        return 0.35 if order >= 3 else 0.05
     return 0.25 if name.startswith(("MIE", "GSAFT")) else 0.02
 
 
@@ -386,6 +400,23 @@ def gsaft_pc_suite(be, oracle, name, n=300):
     sigma_derivs(be, oracle, name, n=100)
     virials(be, oracle, name, n=100)
     if nc >= 2:   # (the cross tables need two components; the isoprops checker indexes [Ncomp][npts] arrays)
+        cross_composition(be, oracle, name, n=60)
+        isoprops(be, oracle, name, n=100)
+
+
+def qcpr_suite(be, oracle, name, n=300):
+    """SURVEY row f4: the quantum-corrected Peng-Robinson model (simple_cubics.hpp:447-557) through every entry point the other cubics are tested on;
+    no virial table (the volume translation forms 1/rho, which has no jet at rho = 0)"""
+    spec = cases.SPECS[name][0]
+    nc = len(cases.SPECS[name][3])
+    z0 = np.array(cases.SPECS[name][3])
+    R = be._R(spec, z0) if hasattr(be, "_R") else be.model(spec).get_R(z0)
+    assert R == spec["model"].get("R / J/mol/K", 8.31446261815324) == oracle.RefModel(spec).get_R(z0)   # catch_test_cubics.cxx:657-664
+    ar_tables(be, oracle, name, n=n)
+    isochoric(be, oracle, name, n=n)
+    atrhoxi(be, oracle, name, n=100)
+    sigma_derivs(be, oracle, name, n=100)
+    if nc >= 2:
         cross_composition(be, oracle, name, n=60)
         isoprops(be, oracle, name, n=100)
 

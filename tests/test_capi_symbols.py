@@ -79,3 +79,11 @@ def test_bad_model_specs_raise():
         with pytest.raises(teqp_b200.TeqpError) as e:
             teqp_b200.make_model(spec)
         assert e.value.code == 30
+    # QCPRAasen: L, M, N of different lengths (simple_cubics.hpp:458-460); an empty kmat, which the reference turns into a 0 x 0 matrix and then
+    # indexes out of bounds (json_tools.hpp:46-48, simple_cubics.hpp:507-516), is refused here; virial coefficients are not offered
+    import cases
+    qc = cases.SPECS["QCPR_H2NE"][0]["model"]
+    for bad in [dict(qc, Ls=[1.0]), dict(qc, kmat=[]), dict(qc, lmat=None), dict(qc, As=[1.0])]:
+        with pytest.raises(teqp_b200.TeqpError) as e:
+            teqp_b200.make_model({"kind": "QCPRAasen", "model": bad})
+        assert e.value.code == 30

@@ -116,6 +116,12 @@ def test_pure_vle(emul, oracle, name):
     assert ps.pure_vle(ps.EmulBackend(emul), oracle, name, n=64) > 0
 
 
+@pytest.mark.parametrize("name", cases.QCPR_CASES)
+def test_qcpr(emul, oracle, name):
+    """kind "QCPRAasen" (quantum-corrected Peng-Robinson with temperature-dependent covolumes and volume translation)"""
+    ps.qcpr_suite(ps.EmulBackend(emul), oracle, name, n=300)
+
+
 @pytest.mark.parametrize("name", cases.GSAFT_PC_CASES)
 def test_genericsaft_pcsaft(emul, oracle, name):
     """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""

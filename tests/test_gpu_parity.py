@@ -342,6 +342,12 @@ def test_pure_vle(be, oracle, name):
     assert ps.pure_vle(be, oracle, name, n=2000) > 0
 
 
+@pytest.mark.parametrize("name", cases.QCPR_CASES)
+def test_qcpr(be, oracle, name):
+    """kind "QCPRAasen" (quantum-corrected Peng-Robinson with temperature-dependent covolumes and volume translation)"""
+    ps.qcpr_suite(be, oracle, name, n=600)
+
+
 @pytest.mark.parametrize("name", cases.GSAFT_PC_CASES)
 def test_genericsaft_pcsaft(be, oracle, name):
     """genericSAFT whose non-polar term is PC-SAFT, with and without association (VERDICT r01 missing #7)"""
