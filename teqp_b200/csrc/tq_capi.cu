@@ -28,6 +28,7 @@ int sm_count() {
 
 bool gerg_try_launch_fused(const Model&, const DeviceBatch&, const IsochoricOut&, const IsoPropsOut&, cudaStream_t);   // tq_gerg.cu
 std::unique_ptr<Model> make_qcpr_model(const Json& spec);   // tq_qcpr.cu
+std::unique_ptr<Model> make_rkpr_model(const Json& spec);   // tq_rkpr.cu
 // ideal-gas kinds (tq_ideal.cu)
 std::unique_ptr<Model> make_ideal_helmholtz_model(const Json& jpures);
 std::unique_ptr<Model> make_gerg_idealgas_model(const std::string& kind, const Json& spec);
@@ -44,6 +45,7 @@ std::unique_ptr<Model> make_model(const Json& j) {
     if (kind == "genericSAFT") return make_genericsaft_model(spec);
     if (kind == "multifluid") return make_multifluid_model(spec);
     if (kind == "QCPRAasen") return make_qcpr_model(spec);
+    if (kind == "RKPRCismondi2005") return make_rkpr_model(spec);
     if (kind == "IdealHelmholtz") return make_ideal_helmholtz_model(spec);
     if (kind == "GERG2008idealgas" || kind == "GERG2004idealgas") return make_gerg_idealgas_model(kind, spec);
     throw InvalidArgument("Don't understand \"kind\" of: " + kind);

@@ -21,6 +21,7 @@
 #include "../../teqp_b200/csrc/tq_assoc.cuh"
 #include "../../teqp_b200/csrc/tq_ideal.cuh"
 #include "../../teqp_b200/csrc/tq_qcpr.cuh"
+#include "../../teqp_b200/csrc/tq_rkpr.cuh"
 #include "../../teqp_b200/csrc/tq_pcassoc.cuh"
 #include "../../teqp_b200/csrc/tq_vle.cuh"
 
@@ -242,6 +243,11 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             generic_table<QcprDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
         }
+        if (fam == "RKPR") {
+            const RkprParams& p = *static_cast<const RkprParams*>(blob);
+            generic_table<RkprDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
 }
@@ -264,6 +270,7 @@ int emul_extras(const char* json, int what, int NT, int ND, long long npts, cons
         if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") TQ_FAM(GsaftDev, GsaftParams, p.mie.nc)
         if (fam == "idealgas" && what == 1) TQ_FAM(IdealDev, IdealParams, p.nc)
         if (fam == "QCPR" && what == 1) TQ_FAM(QcprDev, QcprParams, p.nc)
+        if (fam == "RKPR") TQ_FAM(RkprDev, RkprParams, p.nc)
         if (fam == "genericSAFT-PCSAFT") TQ_FAM(PcAssocDev, PcAssocParams, p.pc.nc)
 #undef TQ_FAM
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
@@ -299,6 +306,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         else if (fam == "PCSAFT") generic_atrhoxi<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "idealgas") generic_atrhoxi<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "QCPR") generic_atrhoxi<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "RKPR") generic_atrhoxi<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three small-jet parts the product launches for this family (GsaftModel::launch_ATrhoXi_table)
@@ -338,6 +346,7 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         if (fam == "cubic" || fam == "vdW") generic_xx<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "idealgas") generic_xx<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "QCPR") generic_xx<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "RKPR") generic_xx<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "PCSAFT") dir_xx<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") dir_xx<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
@@ -361,6 +370,7 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         if (fam == "cubic" || fam == "vdW") generic_ip<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "idealgas") generic_ip<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "QCPR") generic_ip<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "RKPR") generic_ip<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three single-shape parts the product launches for this family (GsaftModel::launch_isoprops)
@@ -411,6 +421,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         if (fam == "cubic" || fam == "vdW") generic_iso<CubicDev>(*static_cast<const CubicParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "idealgas") generic_iso<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "QCPR") generic_iso<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "RKPR") generic_iso<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "genericSAFT-PCSAFT") generic_iso<PcAssocDev>(*static_cast<const PcAssocParams*>(blob), ncomp, npts, T, rhovec, o);

@@ -421,6 +421,23 @@ def qcpr_suite(be, oracle, name, n=300):
         isoprops(be, oracle, name, n=100)
 
 
+def rkpr_suite(be, oracle, name, n=300):
+    """the RK-PR cubic (simple_cubics.hpp:593-690, composition-dependent Delta_1) through every entry point the other cubics are tested
+    on, virial coefficients included (catch_test_cubics.cxx:757-778 checks get_R and a finite B2)"""
+    spec = cases.SPECS[name][0]
+    z0 = np.array(cases.SPECS[name][3])
+    R = be._R(spec, z0) if hasattr(be, "_R") else be.model(spec).get_R(z0)
+    assert R == spec["model"].get("R / J/mol/K", 8.31446261815324) == oracle.RefModel(spec).get_R(z0)
+    ar_tables(be, oracle, name, n=n)
+    isochoric(be, oracle, name, n=n)
+    atrhoxi(be, oracle, name, n=100)
+    sigma_derivs(be, oracle, name, n=100)
+    virials(be, oracle, name, n=100)
+    if z0.size >= 2:
+        cross_composition(be, oracle, name, n=60)
+        isoprops(be, oracle, name, n=100)
+
+
 def idealgas_suite(be, oracle, name, n=300):
     """an ideal-gas kind through every entry point the residual kinds are tested on (the reference serves alpha^ig through the
     same AbstractModel surface: ideal_eosterms.hpp:355-360, GERG.hpp:1214-1223)"""

@@ -87,3 +87,8 @@ def test_bad_model_specs_raise():
         with pytest.raises(teqp_b200.TeqpError) as e:
             teqp_b200.make_model({"kind": "QCPRAasen", "model": bad})
         assert e.value.code == 30
+    rk = cases.SPECS["RKPR_BIN"][0]["model"]
+    for bad in [dict(rk, k=[1.0]), dict(rk, kmat=[]), dict(rk, lmat=[[0.0, 0.0]])]:
+        with pytest.raises(teqp_b200.TeqpError) as e:
+            teqp_b200.make_model({"kind": "RKPRCismondi2005", "model": bad})
+        assert e.value.code == 30

@@ -116,6 +116,12 @@ def test_pure_vle(emul, oracle, name):
     assert ps.pure_vle(ps.EmulBackend(emul), oracle, name, n=64) > 0
 
 
+@pytest.mark.parametrize("name", cases.RKPR_CASES)
+def test_rkpr(emul, oracle, name):
+    """kind "RKPRCismondi2005" (three-parameter cubic with a mole-fraction-averaged Delta_1)"""
+    ps.rkpr_suite(ps.EmulBackend(emul), oracle, name, n=300)
+
+
 @pytest.mark.parametrize("name", cases.QCPR_CASES)
 def test_qcpr(emul, oracle, name):
     """kind "QCPRAasen" (quantum-corrected Peng-Robinson with temperature-dependent covolumes and volume translation)"""
