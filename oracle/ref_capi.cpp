@@ -15,6 +15,7 @@
 #include "teqp/cpp/deriv_adapter.hpp"
 #include "teqp/models/vdW.hpp"
 #include "teqp/models/cubics/simple_cubics.hpp"
+#include "teqp/models/cubics/advancedmixing_cubics.hpp"
 #include "teqp/models/GERG/GERG.hpp"
 #include "teqp/models/pcsaft.hpp"
 #include "teqp/models/multifluid.hpp"
@@ -69,6 +70,7 @@ std::unique_ptr<AbstractModel> build(const nlohmann::json& j, std::string& kind)
     if (kind == "GERG2008idealgas") return make_GERG2008idealgas(spec);
     if (kind == "IdealHelmholtz") return make_IdealHelmholtz(spec);
     if (kind == "QCPRAasen") return make_owned(QuantumCorrectedPR(spec));   // interface/CPP/teqp_impl_factory.cpp:60
+    if (kind == "advancedPRaEres") return make_owned(make_AdvancedPRaEres(spec));   // interface/CPP/teqp_impl_factory.cpp:59
     if (kind == "RKPRCismondi2005") return make_owned(RKPRCismondi2005(spec));   // interface/CPP/teqp_impl_factory.cpp:61
     throw std::invalid_argument("Don't understand \"kind\" of: " + kind);
 }
@@ -319,6 +321,7 @@ int ref_lnphi_family(void* h, int what, long long npts, const double* T, const d
     else if (rm->kind == "IdealHelmholtz") { const auto& m = get_model_cref<IdealHelmholtz>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "QCPRAasen") { const auto& m = get_model_cref<QuantumCorrectedPR>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else if (rm->kind == "RKPRCismondi2005") { const auto& m = get_model_cref<RKPRCismondi2005>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
+    else if (rm->kind == "advancedPRaEres") { const auto& m = get_model_cref<advancedPRaEres_t>(am); one = [&m, what](double T_, const Eigen::ArrayXd& r, Eigen::ArrayXd& v) { lnphi_point(m, what, T_, r, v); }; }
     else { put_err("ln(phi) family: kind not wired in the oracle: " + rm->kind, err, errlen); return 200; }
     return parallel_points(npts, nthreads, err, errlen, [&](long long k) {
         thread_local Eigen::ArrayXd r, v; if (r.size() != ncomp) r.resize(ncomp);

@@ -29,6 +29,7 @@ int sm_count() {
 bool gerg_try_launch_fused(const Model&, const DeviceBatch&, const IsochoricOut&, const IsoPropsOut&, cudaStream_t);   // tq_gerg.cu
 std::unique_ptr<Model> make_qcpr_model(const Json& spec);   // tq_qcpr.cu
 std::unique_ptr<Model> make_rkpr_model(const Json& spec);   // tq_rkpr.cu
+std::unique_ptr<Model> make_apr_model(const Json& spec);    // tq_apr.cu
 // ideal-gas kinds (tq_ideal.cu)
 std::unique_ptr<Model> make_ideal_helmholtz_model(const Json& jpures);
 std::unique_ptr<Model> make_gerg_idealgas_model(const std::string& kind, const Json& spec);
@@ -46,6 +47,7 @@ std::unique_ptr<Model> make_model(const Json& j) {
     if (kind == "multifluid") return make_multifluid_model(spec);
     if (kind == "QCPRAasen") return make_qcpr_model(spec);
     if (kind == "RKPRCismondi2005") return make_rkpr_model(spec);
+    if (kind == "advancedPRaEres") return make_apr_model(spec);
     if (kind == "IdealHelmholtz") return make_ideal_helmholtz_model(spec);
     if (kind == "GERG2008idealgas" || kind == "GERG2004idealgas") return make_gerg_idealgas_model(kind, spec);
     throw InvalidArgument("Don't understand \"kind\" of: " + kind);

@@ -22,6 +22,7 @@
 #include "../../teqp_b200/csrc/tq_ideal.cuh"
 #include "../../teqp_b200/csrc/tq_qcpr.cuh"
 #include "../../teqp_b200/csrc/tq_rkpr.cuh"
+#include "../../teqp_b200/csrc/tq_apr.cuh"
 #include "../../teqp_b200/csrc/tq_pcassoc.cuh"
 #include "../../teqp_b200/csrc/tq_vle.cuh"
 
@@ -248,6 +249,11 @@ int emul_ar_table(const char* json, int mode, int NT, int ND, long long npts, co
             generic_table<RkprDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
             return 0;
         }
+        if (fam == "advancedPRaEres") {
+            const AprParams& p = *static_cast<const AprParams*>(blob);
+            generic_table<AprDev>(p, p.nc, NT, ND, npts, T, rho, x, xs, out);
+            return 0;
+        }
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
     } catch (const std::exception& e) { put(e.what(), err, errlen); return 1; }
 }
@@ -271,6 +277,7 @@ int emul_extras(const char* json, int what, int NT, int ND, long long npts, cons
         if (fam == "idealgas" && what == 1) TQ_FAM(IdealDev, IdealParams, p.nc)
         if (fam == "QCPR" && what == 1) TQ_FAM(QcprDev, QcprParams, p.nc)
         if (fam == "RKPR") TQ_FAM(RkprDev, RkprParams, p.nc)
+        if (fam == "advancedPRaEres") TQ_FAM(AprDev, AprParams, p.nc)
         if (fam == "genericSAFT-PCSAFT") TQ_FAM(PcAssocDev, PcAssocParams, p.pc.nc)
 #undef TQ_FAM
         throw InvalidArgument("family not wired in the emulation harness: " + fam);
@@ -307,6 +314,7 @@ int emul_ATrhoXi_table(const char* json, long long npts, const double* T, const 
         else if (fam == "idealgas") generic_atrhoxi<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "QCPR") generic_atrhoxi<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "RKPR") generic_atrhoxi<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rho, x, out);
+        else if (fam == "advancedPRaEres") generic_atrhoxi<AprDev>(*static_cast<const AprParams*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_atrhoxi<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three small-jet parts the product launches for this family (GsaftModel::launch_ATrhoXi_table)
@@ -347,6 +355,7 @@ int emul_cross_table(const char* json, int which, int i, int j, int k, long long
         else if (fam == "idealgas") generic_xx<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "QCPR") generic_xx<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "RKPR") generic_xx<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
+        else if (fam == "advancedPRaEres") generic_xx<AprDev>(*static_cast<const AprParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam.rfind("GERG", 0) == 0 || fam == "multifluid") generic_xx<GergJetDev>(*static_cast<const GergProgram*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "PCSAFT") dir_xx<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") dir_xx<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, which, i, j, k, npts, T, rho, x, out);
@@ -371,6 +380,7 @@ int emul_isoprops(const char* json, long long npts, const double* T, const doubl
         else if (fam == "idealgas") generic_ip<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "QCPR") generic_ip<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "RKPR") generic_ip<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "advancedPRaEres") generic_ip<AprDev>(*static_cast<const AprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_ip<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") {
             // the three single-shape parts the product launches for this family (GsaftModel::launch_isoprops)
@@ -422,6 +432,7 @@ int emul_isochoric(const char* json, long long npts, const double* T, const doub
         else if (fam == "idealgas") generic_iso<IdealDev>(*static_cast<const IdealParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "QCPR") generic_iso<QcprDev>(*static_cast<const QcprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "RKPR") generic_iso<RkprDev>(*static_cast<const RkprParams*>(blob), ncomp, npts, T, rhovec, o);
+        else if (fam == "advancedPRaEres") generic_iso<AprDev>(*static_cast<const AprParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "PCSAFT") generic_iso<PcsaftDev>(*static_cast<const PcsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "SAFT-VR-Mie" || fam == "genericSAFT") generic_iso<GsaftDev>(*static_cast<const GsaftParams*>(blob), ncomp, npts, T, rhovec, o);
         else if (fam == "genericSAFT-PCSAFT") generic_iso<PcAssocDev>(*static_cast<const PcAssocParams*>(blob), ncomp, npts, T, rhovec, o);

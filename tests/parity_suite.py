@@ -421,6 +421,22 @@ def qcpr_suite(be, oracle, name, n=300):
         isoprops(be, oracle, name, n=100)
 
 
+def apr_suite(be, oracle, name, n=300):
+    """Peng-Robinson with the EoS/aE mixing rule and a Wilson residual term (advancedmixing_cubics.hpp:53-218) through every entry
+    point the other cubics are tested on (catch_test_cubics.cxx:716-743 checks that it builds and get_R)"""
+    spec = cases.SPECS[name][0]
+    z0 = np.array(cases.SPECS[name][3])
+    R = be._R(spec, z0) if hasattr(be, "_R") else be.model(spec).get_R(z0)
+    assert R == spec["model"]["options"].get("R / J/mol/K", 8.31446261815324) == oracle.RefModel(spec).get_R(z0)
+    ar_tables(be, oracle, name, n=n)
+    isochoric(be, oracle, name, n=n)
+    atrhoxi(be, oracle, name, n=100)
+    sigma_derivs(be, oracle, name, n=100)
+    virials(be, oracle, name, n=100)
+    cross_composition(be, oracle, name, n=60)
+    isoprops(be, oracle, name, n=100)
+
+
 def rkpr_suite(be, oracle, name, n=300):
     """the RK-PR cubic (simple_cubics.hpp:593-690, composition-dependent Delta_1) through every entry point the other cubics are tested
     on, virial coefficients included (catch_test_cubics.cxx:757-778 checks get_R and a finite B2)"""

@@ -92,3 +92,11 @@ def test_bad_model_specs_raise():
         with pytest.raises(teqp_b200.TeqpError) as e:
             teqp_b200.make_model({"kind": "RKPRCismondi2005", "model": bad})
         assert e.value.code == 30
+    # advancedPRaEres: unknown aE model / alpha type / b rule; a one-component spec is refused as by the reference (its factory passes a 2 x 2 lmat)
+    ap = cases.SPECS["APR_CO2_N2"][0]["model"]
+    one = {"Tcrit / K": [304.21], "pcrit / Pa": [7.383e6], "alphas": [ap["alphas"][0]], "aresmodel": {"type": "Wilson", "m": [[0.0]], "n": [[0.0]]}, "options": ap["options"]}
+    for bad in [dict(ap, aresmodel={"type": "NRTL"}), dict(ap, alphas=[{"type": "X"}, {"type": "X"}]), dict(ap, options=dict(ap["options"], brule="Cubic")),
+                dict(ap, options={"s": 2.0, "brule": "Linear"}), one]:
+        with pytest.raises(teqp_b200.TeqpError) as e:
+            teqp_b200.make_model({"kind": "advancedPRaEres", "model": bad})
+        assert e.value.code == 30

@@ -116,6 +116,12 @@ def test_pure_vle(emul, oracle, name):
     assert ps.pure_vle(ps.EmulBackend(emul), oracle, name, n=64) > 0
 
 
+@pytest.mark.parametrize("name", cases.APR_CASES)
+def test_advancedPRaEres(emul, oracle, name):
+    """kind "advancedPRaEres" (EoS/aE mixing rule with a Wilson residual excess Helmholtz energy)"""
+    ps.apr_suite(ps.EmulBackend(emul), oracle, name, n=300)
+
+
 @pytest.mark.parametrize("name", cases.RKPR_CASES)
 def test_rkpr(emul, oracle, name):
     """kind "RKPRCismondi2005" (three-parameter cubic with a mole-fraction-averaged Delta_1)"""

@@ -342,6 +342,12 @@ def test_pure_vle(be, oracle, name):
     assert ps.pure_vle(be, oracle, name, n=2000) > 0
 
 
+@pytest.mark.parametrize("name", cases.APR_CASES)
+def test_advancedPRaEres(be, oracle, name):
+    """kind "advancedPRaEres" (EoS/aE mixing rule with a Wilson residual excess Helmholtz energy)"""
+    ps.apr_suite(be, oracle, name, n=600)
+
+
 @pytest.mark.parametrize("name", cases.RKPR_CASES)
 def test_rkpr(be, oracle, name):
     """kind "RKPRCismondi2005" (three-parameter cubic with a mole-fraction-averaged Delta_1)"""
